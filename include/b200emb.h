@@ -1,0 +1,152 @@
+/* b200emb.h — C ABI of the B200 (sm_100a) sparse-embedding kernels.
+ *
+ * Drop-in boundary for PaddlePaddle Fluid's sparse-embedding hot path: each entry point is
+ * what the body of one reference `OpKernel<T>::Compute` (or one math functor) would call.
+ * Citations are relative to /root/reference/paddle/fluid/.
+ *
+ * Conventions (all entry points):
+ *   - every pointer is a DEVICE pointer on the current device unless named `*_host`;
+ *   - `stream` is a cudaStream_t passed as void*; work is only enqueued, never synchronised;
+ *   - nothing is allocated: temporaries live in the caller-provided `workspace`
+ *     (size from b200emb_workspace_bytes, 256-byte aligned; the framework hands it out from
+ *     its own allocator the way MergeAdd's temporary SelectedRows is, selected_rows_functor.h:63-68);
+ *   - return value: 0 on success, a negative B200EMB_E_* code otherwise (never throws);
+ *   - ids / rows are int64 (lookup_table_op.h:44); tables are float or double (`_f32` / `_f64`);
+ *   - limits: height < 2^32-1, N < 2^30 (the reference caps at 2^31 via int casts,
+ *     platform/for_range.h:61).
+ *   - `status` (nullable int32*): device word the kernels OR error bits into instead of the
+ *     reference's PADDLE_ENFORCE / device assert: bit0 = lookup id outside [0,height)
+ *     (lookup_table_op.h:59-60), bit1 = gradient row outside [0,height) (sgd_op.h:75-76).
+ *     Offending rows are skipped (lookup writes zeros).
+ *
+ * flags:
+ *   B200EMB_DETERMINISTIC  bit-exact order mode: every duplicate is accumulated in input order
+ *                          exactly like the reference CPU loops (MergeAdd: from +0.0,
+ *                          selected_rows_functor.cc:214-225; SGD: one p-=lr*g per occurrence,
+ *                          sgd_op.h:74-80).  Default (fast) mode reduces duplicates with a
+ *                          fixed-shape tree (run-to-run deterministic, differs in rounding).
+ *   B200EMB_PLAN_READY     the workspace already holds the sort plan of exactly these
+ *                          rows (b200emb_plan_rows was run on it): skip the sort.
+ */
+#ifndef B200EMB_H_
+#define B200EMB_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200EMB_OK 0
+#define B200EMB_E_INVALID (-1)     /* bad argument (null pointer, negative size, D<=0 ...) */
+#define B200EMB_E_WORKSPACE (-2)   /* workspace missing, misaligned or too small */
+#define B200EMB_E_CUDA (-3)        /* a CUDA call / launch failed (see b200emb_last_cuda_error) */
+#define B200EMB_E_UNSUPPORTED (-4) /* size beyond the documented limits */
+
+#define B200EMB_DETERMINISTIC 1u
+#define B200EMB_PLAN_READY 2u
+
+#define B200EMB_STATUS_BAD_LOOKUP_ID 1
+#define B200EMB_STATUS_BAD_GRAD_ROW 2
+
+int b200emb_abi_version(void);
+/* cudaError_t of the last failing CUDA call made by this library on the calling thread. */
+int b200emb_last_cuda_error(void);
+
+/* Bytes of workspace the sort/merge/update entry points need for n rows of width d
+ * (elem_size 4 or 8).  Pure host arithmetic. */
+size_t b200emb_workspace_bytes(int64_t n, int64_t d, int64_t elem_size);
+
+/* lookup_table forward — replaces LookupTableCUDAKernel::Compute + LookupTable<>
+ * (operators/lookup_table_op.cu:24-50,72-103; CPU semantics lookup_table_op.h:36-84):
+ * out[k,:] = (ids[k]==padding_idx) ? 0 : table[ids[k],:].  padding_idx = -1 means none. */
+int b200emb_lookup_table_f32(const float* table, int64_t height, int64_t d, const int64_t* ids,
+                             int64_t n, int64_t padding_idx, float* out, int32_t* status,
+                             void* stream);
+int b200emb_lookup_table_f64(const double* table, int64_t height, int64_t d, const int64_t* ids,
+                             int64_t n, int64_t padding_idx, double* out, int32_t* status,
+                             void* stream);
+
+/* lookup_table_grad, sparse branch — replaces LookupTableGradCUDAKernel's is_sparse path
+ * (operators/lookup_table_op.cu:114-147; lookup_table_op.h:106-134): rows = ids verbatim,
+ * value = copy of dOut.  Either output may alias its input (then that copy is skipped). */
+int b200emb_lookup_table_grad_sparse_f32(const int64_t* ids, const float* d_out, int64_t n,
+                                         int64_t d, int64_t* rows, float* value, void* stream);
+int b200emb_lookup_table_grad_sparse_f64(const int64_t* ids, const double* d_out, int64_t n,
+                                         int64_t d, int64_t* rows, double* value, void* stream);
+
+/* `sum` over SelectedRows / SelectedRowsAddTo — replaces operators/sum_op.h:71-145 +
+ * math/selected_rows_functor.cu:142-174: appends n_in rows at row offset `row_offset`
+ * of (out_rows, out_value).  elem_size = sizeof(T). */
+int b200emb_selected_rows_add_to(const int64_t* in_rows, const void* in_value, int64_t n_in,
+                                 int64_t d, int64_t elem_size, int64_t* out_rows,
+                                 void* out_value, int64_t row_offset, void* stream);
+
+/* Sort plan: stable sort-by-id of `rows` into the workspace (sorted keys + original
+ * positions).  Lets the caller overlap the sort with other work (e.g. the forward gather
+ * on another stream) and then run merge_add / sparse_sgd / sparse_adam with
+ * B200EMB_PLAN_READY.  No counterpart in the reference (its MergeAdd builds a std::set on the
+ * host: math/selected_rows_functor.cu:265-267). */
+int b200emb_plan_rows(const int64_t* rows, int64_t n, int64_t height, void* workspace,
+                      size_t workspace_bytes, int32_t* status, void* stream);
+
+/* scatter::MergeAdd — replaces math/selected_rows_functor.cu:235-297 (CPU semantics
+ * selected_rows_functor.cc:193-228): out_rows = ascending unique rows, out_value[u,:] = sum of
+ * the input rows with that id.  out_rows/out_value must hold n rows; *n_unique (device int64)
+ * receives U.  */
+int b200emb_merge_add_f32(const int64_t* rows, const float* value, int64_t n, int64_t d,
+                          int64_t height, int64_t* out_rows, float* out_value,
+                          int64_t* n_unique, void* workspace, size_t workspace_bytes,
+                          unsigned flags, int32_t* status, void* stream);
+int b200emb_merge_add_f64(const int64_t* rows, const double* value, int64_t n, int64_t d,
+                          int64_t height, int64_t* out_rows, double* out_value,
+                          int64_t* n_unique, void* workspace, size_t workspace_bytes,
+                          unsigned flags, int32_t* status, void* stream);
+
+/* SelectedRowsAddToTensor — replaces math/selected_rows_functor.cu:181-226 (CPU
+ * selected_rows_functor.cc:153-178): tensor[rows[i],:] += value[i,:], duplicates accumulate. */
+int b200emb_selected_rows_add_to_tensor_f32(const int64_t* rows, const float* value, int64_t n,
+                                            int64_t d, int64_t height, float* tensor,
+                                            void* workspace, size_t workspace_bytes,
+                                            unsigned flags, int32_t* status, void* stream);
+int b200emb_selected_rows_add_to_tensor_f64(const int64_t* rows, const double* value, int64_t n,
+                                            int64_t d, int64_t height, double* tensor,
+                                            void* workspace, size_t workspace_bytes,
+                                            unsigned flags, int32_t* status, void* stream);
+
+/* sparse SGD (dense Param, SelectedRows Grad), in place — replaces SGDOpCUDAKernel's
+ * SelectedRows branch + SparseSGDFunctorKernel (operators/sgd_op.cu:36-53,80-106; CPU
+ * semantics sgd_op.h:47-81).  `lr` is the 1-element LearningRate tensor on the device.
+ * Duplicate-row reduction is fused with the update: gradient rows are read once and the
+ * merged rows never reach memory. */
+int b200emb_sparse_sgd_f32(float* param, int64_t height, int64_t d, const int64_t* rows,
+                           const float* grad, int64_t n, const float* lr, void* workspace,
+                           size_t workspace_bytes, unsigned flags, int32_t* status,
+                           void* stream);
+int b200emb_sparse_sgd_f64(double* param, int64_t height, int64_t d, const int64_t* rows,
+                           const double* grad, int64_t n, const double* lr, void* workspace,
+                           size_t workspace_bytes, unsigned flags, int32_t* status,
+                           void* stream);
+
+/* sparse (lazy) Adam, in place — replaces AdamOpKernel's SelectedRows branch =
+ * scatter::MergeAdd + SparseAdamFunctor via ForRange (operators/adam_op.h:158-220,282-321).
+ * lr, beta1_pow, beta2_pow are the 1-element device tensors; beta1/beta2/epsilon are the
+ * float attrs (adam_op.cc:99-112), cast to T as adam_op.h:233-235 does. */
+int b200emb_sparse_adam_f32(float* param, float* moment1, float* moment2, int64_t height,
+                            int64_t d, const int64_t* rows, const float* grad, int64_t n,
+                            const float* lr, const float* beta1_pow, const float* beta2_pow,
+                            float beta1, float beta2, float epsilon, void* workspace,
+                            size_t workspace_bytes, unsigned flags, int32_t* status,
+                            void* stream);
+int b200emb_sparse_adam_f64(double* param, double* moment1, double* moment2, int64_t height,
+                            int64_t d, const int64_t* rows, const double* grad, int64_t n,
+                            const double* lr, const double* beta1_pow, const double* beta2_pow,
+                            float beta1, float beta2, float epsilon, void* workspace,
+                            size_t workspace_bytes, unsigned flags, int32_t* status,
+                            void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200EMB_H_ */

@@ -1,0 +1,210 @@
+"""ctypes binding of include/b200emb.h over torch CUDA tensors.
+
+torch is used for device memory and streams only; every computation is a kernel of
+libb200emb.so.  Missing library or missing GPU raises — there is no fallback path.
+"""
+import ctypes
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "libb200emb.so")
+
+DETERMINISTIC = 1
+PLAN_READY = 2
+
+_ERRORS = {-1: "invalid argument", -2: "workspace missing/misaligned/too small",
+           -3: "CUDA error", -4: "size beyond supported limits"}
+
+EXPORTS = [
+    "b200emb_abi_version", "b200emb_last_cuda_error", "b200emb_workspace_bytes",
+    "b200emb_lookup_table_f32", "b200emb_lookup_table_f64",
+    "b200emb_lookup_table_grad_sparse_f32", "b200emb_lookup_table_grad_sparse_f64",
+    "b200emb_selected_rows_add_to", "b200emb_plan_rows",
+    "b200emb_merge_add_f32", "b200emb_merge_add_f64",
+    "b200emb_selected_rows_add_to_tensor_f32", "b200emb_selected_rows_add_to_tensor_f64",
+    "b200emb_sparse_sgd_f32", "b200emb_sparse_sgd_f64",
+    "b200emb_sparse_adam_f32", "b200emb_sparse_adam_f64",
+]
+
+_lib = None
+
+
+class B200EmbError(RuntimeError):
+    pass
+
+
+def lib():
+    """Load libb200emb.so; raise loudly when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB_PATH):
+            raise B200EmbError(
+                "libb200emb.so not built (run __graft_entry__.build()); there is no CPU fallback")
+        _lib = ctypes.CDLL(_LIB_PATH)
+        _lib.b200emb_workspace_bytes.restype = ctypes.c_size_t
+        _lib.b200emb_workspace_bytes.argtypes = [ctypes.c_int64] * 3
+    return _lib
+
+
+def _check(rc, what):
+    if rc != 0:
+        extra = ""
+        if rc == -3:
+            extra = " (cudaError %d)" % lib().b200emb_last_cuda_error()
+        raise B200EmbError("%s failed: %s%s" % (what, _ERRORS.get(rc, rc), extra))
+
+
+def _ptr(t):
+    return ctypes.c_void_p(0 if t is None else t.data_ptr())
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _sfx(dtype):
+    if dtype == torch.float32:
+        return "f32"
+    if dtype == torch.float64:
+        return "f64"
+    raise TypeError("tables are float32 or float64 (lookup_table_op.cu:175-180), got %s" % dtype)
+
+
+def _need_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise B200EmbError("b200emb ops need CUDA tensors; there is no CPU fallback")
+        if t is not None and not t.is_contiguous():
+            raise B200EmbError("b200emb ops need contiguous tensors")
+
+
+def workspace_bytes(n, d, elem_size=4):
+    return int(lib().b200emb_workspace_bytes(int(n), int(d), int(elem_size)))
+
+
+def alloc_workspace(n, d, elem_size=4, device="cuda"):
+    nbytes = max(workspace_bytes(n, d, elem_size), 256)
+    return torch.empty(nbytes, dtype=torch.uint8, device=device)
+
+
+def new_status(device="cuda"):
+    return torch.zeros(1, dtype=torch.int32, device=device)
+
+
+def lookup_table(table, ids, padding_idx=-1, out=None, status=None):
+    """Out[k,:] = W[ids[k],:] (padding rows zero). ids: int64, any shape; returns [ids.numel(), D]."""
+    _need_cuda(table, ids, out, status)
+    assert ids.dtype == torch.int64
+    v, d = table.shape
+    n = ids.numel()
+    if out is None:
+        out = torch.empty((n, d), dtype=table.dtype, device=table.device)
+    fn = getattr(lib(), "b200emb_lookup_table_" + _sfx(table.dtype))
+    _check(fn(_ptr(table), ctypes.c_int64(v), ctypes.c_int64(d), _ptr(ids), ctypes.c_int64(n),
+              ctypes.c_int64(padding_idx), _ptr(out), _ptr(status), _stream()), "lookup_table")
+    return out
+
+
+def lookup_table_grad_sparse(ids, d_out, rows=None, value=None):
+    """SelectedRows grad: rows = ids verbatim, value = copy of dOut (pass rows=ids/value=d_out to alias)."""
+    _need_cuda(ids, d_out, rows, value)
+    n = ids.numel()
+    d = d_out.shape[-1]
+    if rows is None:
+        rows = torch.empty(n, dtype=torch.int64, device=ids.device)
+    if value is None:
+        value = torch.empty((n, d), dtype=d_out.dtype, device=d_out.device)
+    fn = getattr(lib(), "b200emb_lookup_table_grad_sparse_" + _sfx(d_out.dtype))
+    _check(fn(_ptr(ids), _ptr(d_out), ctypes.c_int64(n), ctypes.c_int64(d), _ptr(rows), _ptr(value),
+              _stream()), "lookup_table_grad")
+    return rows, value
+
+
+def sum_selected_rows(inputs):
+    """`sum` over SelectedRows: concat (rows, value) pairs, skipping empty ones (sum_op.h:71-145)."""
+    total = sum(int(r.numel()) for r, _ in inputs)
+    first = next((v for r, v in inputs if r.numel() > 0), inputs[-1][1])
+    d = first.shape[1]
+    out_rows = torch.empty(total, dtype=torch.int64, device=first.device)
+    out_value = torch.empty((total, d), dtype=first.dtype, device=first.device)
+    off = 0
+    for r, v in inputs:
+        n = int(r.numel())
+        if n == 0:
+            continue
+        _need_cuda(r, v)
+        _check(lib().b200emb_selected_rows_add_to(
+            _ptr(r), _ptr(v), ctypes.c_int64(n), ctypes.c_int64(d), ctypes.c_int64(v.element_size()),
+            _ptr(out_rows), _ptr(out_value), ctypes.c_int64(off), _stream()), "selected_rows_add_to")
+        off += n
+    return out_rows, out_value
+
+
+def plan_rows(rows, height, workspace, status=None):
+    _need_cuda(rows, workspace, status)
+    _check(lib().b200emb_plan_rows(_ptr(rows), ctypes.c_int64(rows.numel()), ctypes.c_int64(height),
+                                   _ptr(workspace), ctypes.c_size_t(workspace.numel()), _ptr(status),
+                                   _stream()), "plan_rows")
+
+
+def merge_add(rows, value, height, workspace=None, flags=0, status=None):
+    """scatter::MergeAdd -> (out_rows[n], out_value[n,d], n_unique[1] int64); only the first U rows are meaningful."""
+    _need_cuda(rows, value, workspace, status)
+    n, d = value.shape
+    if workspace is None:
+        workspace = alloc_workspace(n, d, value.element_size(), value.device)
+    out_rows = torch.empty(n, dtype=torch.int64, device=value.device)
+    out_value = torch.empty((n, d), dtype=value.dtype, device=value.device)
+    n_unique = torch.zeros(1, dtype=torch.int64, device=value.device)
+    fn = getattr(lib(), "b200emb_merge_add_" + _sfx(value.dtype))
+    _check(fn(_ptr(rows), _ptr(value), ctypes.c_int64(n), ctypes.c_int64(d), ctypes.c_int64(height),
+              _ptr(out_rows), _ptr(out_value), _ptr(n_unique), _ptr(workspace),
+              ctypes.c_size_t(workspace.numel()), ctypes.c_uint(flags), _ptr(status), _stream()),
+           "merge_add")
+    return out_rows, out_value, n_unique
+
+
+def selected_rows_add_to_tensor(rows, value, tensor, workspace=None, flags=0, status=None):
+    _need_cuda(rows, value, tensor, workspace, status)
+    n, d = value.shape
+    if workspace is None:
+        workspace = alloc_workspace(n, d, value.element_size(), value.device)
+    fn = getattr(lib(), "b200emb_selected_rows_add_to_tensor_" + _sfx(value.dtype))
+    _check(fn(_ptr(rows), _ptr(value), ctypes.c_int64(n), ctypes.c_int64(d),
+              ctypes.c_int64(tensor.shape[0]), _ptr(tensor), _ptr(workspace),
+              ctypes.c_size_t(workspace.numel()), ctypes.c_uint(flags), _ptr(status), _stream()),
+           "selected_rows_add_to_tensor")
+    return tensor
+
+
+def sparse_sgd(param, rows, grad, lr, workspace=None, flags=0, status=None):
+    """In-place sparse SGD. lr: 1-element device tensor (the LearningRate var)."""
+    _need_cuda(param, rows, grad, lr, workspace, status)
+    n = rows.numel()
+    v, d = param.shape
+    if workspace is None:
+        workspace = alloc_workspace(n, d, param.element_size(), param.device)
+    fn = getattr(lib(), "b200emb_sparse_sgd_" + _sfx(param.dtype))
+    _check(fn(_ptr(param), ctypes.c_int64(v), ctypes.c_int64(d), _ptr(rows), _ptr(grad),
+              ctypes.c_int64(n), _ptr(lr), _ptr(workspace), ctypes.c_size_t(workspace.numel()),
+              ctypes.c_uint(flags), _ptr(status), _stream()), "sparse_sgd")
+    return param
+
+
+def sparse_adam(param, moment1, moment2, rows, grad, lr, beta1_pow, beta2_pow, beta1=0.9, beta2=0.999,
+                epsilon=1e-8, workspace=None, flags=0, status=None):
+    """In-place sparse (lazy) Adam = MergeAdd fused with SparseAdamFunctor."""
+    _need_cuda(param, moment1, moment2, rows, grad, lr, beta1_pow, beta2_pow, workspace, status)
+    n = rows.numel()
+    v, d = param.shape
+    if workspace is None:
+        workspace = alloc_workspace(n, d, param.element_size(), param.device)
+    fn = getattr(lib(), "b200emb_sparse_adam_" + _sfx(param.dtype))
+    _check(fn(_ptr(param), _ptr(moment1), _ptr(moment2), ctypes.c_int64(v), ctypes.c_int64(d),
+              _ptr(rows), _ptr(grad), ctypes.c_int64(n), _ptr(lr), _ptr(beta1_pow), _ptr(beta2_pow),
+              ctypes.c_float(beta1), ctypes.c_float(beta2), ctypes.c_float(epsilon), _ptr(workspace),
+              ctypes.c_size_t(workspace.numel()), ctypes.c_uint(flags), _ptr(status), _stream()),
+           "sparse_adam")
+    return param

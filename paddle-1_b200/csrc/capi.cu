@@ -1,0 +1,215 @@
+// capi.cu — the extern "C" boundary declared in include/b200emb.h.
+// Argument checks, workspace carving and launch sequencing only; kernels live in
+// gather.cu / sort.cu / segreduce.cu.  Nothing here allocates or synchronises.
+#include "../../include/b200emb.h"
+
+#include "common.cuh"
+#include "internal.h"
+
+using namespace b200emb;
+
+namespace {
+thread_local int g_last_cuda_error = 0;
+
+int fail_cuda(cudaError_t e) {
+  g_last_cuda_error = static_cast<int>(e);
+  return B200EMB_E_CUDA;
+}
+
+int check_sizes(int64_t n, int64_t d, int64_t height) {
+  if (n < 0 || d <= 0 || height <= 0) return B200EMB_E_INVALID;
+  if (n >= (1LL << 30) || height >= 0xFFFFFFFFLL || d >= (1LL << 31)) return B200EMB_E_UNSUPPORTED;
+  return B200EMB_OK;
+}
+
+int check_workspace(const void* ws, size_t ws_bytes, const Workspace& L) {
+  if (ws == nullptr || (reinterpret_cast<uintptr_t>(ws) & 255u) != 0) return B200EMB_E_WORKSPACE;
+  if (ws_bytes < L.total) return B200EMB_E_WORKSPACE;
+  return B200EMB_OK;
+}
+
+// Shared driver of merge_add / add_to_tensor / sgd / adam.
+template <typename T>
+int run_update(const int64_t* rows, const T* value, int64_t n, int64_t d, int64_t height,
+               UpdateArgs<T> args, int64_t* out_rows, int64_t* n_unique, void* workspace,
+               size_t workspace_bytes, unsigned flags, int32_t* status, void* stream,
+               bool pointers_ok) {
+  int rc = check_sizes(n, d, height);
+  if (rc != B200EMB_OK) return rc;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (n == 0) {  // empty SelectedRows is legal everywhere (sgd_op.h:56-58, adam_op.h:285-288)
+    if (n_unique) {
+      cudaError_t e = cudaMemsetAsync(n_unique, 0, sizeof(int64_t), s);
+      if (e != cudaSuccess) return fail_cuda(e);
+    }
+    return B200EMB_OK;
+  }
+  if (!pointers_ok || rows == nullptr || value == nullptr || args.param == nullptr)
+    return B200EMB_E_INVALID;
+  const Workspace L = make_workspace(n, d, sizeof(T));
+  rc = check_workspace(workspace, workspace_bytes, L);
+  if (rc != B200EMB_OK) return rc;
+  char* ws = static_cast<char*>(workspace);
+  const bool det = (flags & B200EMB_DETERMINISTIC) != 0;
+  SortedPlan plan;
+  cudaError_t e;
+  if (flags & B200EMB_PLAN_READY) {
+    plan = plan_view(height, ws, L);
+  } else {
+    e = launch_plan(rows, n, height, ws, L, status, s, &plan);
+    if (e != cudaSuccess) return fail_cuda(e);
+  }
+  if (det || args.op == UpdateOp::kMergeAdd) {
+    e = launch_head_scan(plan, n, static_cast<uint32_t>(height), ws, L, out_rows, n_unique, s);
+    if (e != cudaSuccess) return fail_cuda(e);
+    args.uidx = reinterpret_cast<const uint32_t*>(ws + L.off_uidx);
+  }
+  e = launch_update<T>(plan, value, n, d, height, args, det, ws, L, status, s);
+  if (e != cudaSuccess) return fail_cuda(e);
+  return B200EMB_OK;
+}
+
+template <typename T>
+int run_lookup(const T* table, int64_t height, int64_t d, const int64_t* ids, int64_t n,
+               int64_t padding_idx, T* out, int32_t* status, void* stream) {
+  int rc = check_sizes(n, d, height);
+  if (rc != B200EMB_OK) return rc;
+  if (n == 0) return B200EMB_OK;
+  if (!table || !ids || !out) return B200EMB_E_INVALID;
+  cudaError_t e = launch_gather<T>(table, height, d, ids, n, padding_idx, out, status,
+                                   static_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? B200EMB_OK : fail_cuda(e);
+}
+
+template <typename T>
+int run_grad_sparse(const int64_t* ids, const T* d_out, int64_t n, int64_t d, int64_t* rows,
+                    T* value, void* stream) {
+  if (n < 0 || d <= 0) return B200EMB_E_INVALID;
+  if (n == 0) return B200EMB_OK;
+  if (!ids || !d_out || !rows || !value) return B200EMB_E_INVALID;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  cudaError_t e = cudaSuccess;
+  if (rows != ids) e = cudaMemcpyAsync(rows, ids, sizeof(int64_t) * n, cudaMemcpyDeviceToDevice, s);
+  if (e == cudaSuccess && value != d_out)
+    e = cudaMemcpyAsync(value, d_out, sizeof(T) * n * d, cudaMemcpyDeviceToDevice, s);
+  return e == cudaSuccess ? B200EMB_OK : fail_cuda(e);
+}
+}  // namespace
+
+extern "C" {
+
+int b200emb_abi_version(void) { return 1; }
+int b200emb_last_cuda_error(void) { return g_last_cuda_error; }
+
+size_t b200emb_workspace_bytes(int64_t n, int64_t d, int64_t elem_size) {
+  if (n < 0 || d <= 0 || (elem_size != 4 && elem_size != 8)) return 0;
+  return make_workspace(n, d, elem_size).total;
+}
+
+int b200emb_lookup_table_f32(const float* table, int64_t height, int64_t d, const int64_t* ids,
+                             int64_t n, int64_t padding_idx, float* out, int32_t* status,
+                             void* stream) {
+  return run_lookup<float>(table, height, d, ids, n, padding_idx, out, status, stream);
+}
+int b200emb_lookup_table_f64(const double* table, int64_t height, int64_t d, const int64_t* ids,
+                             int64_t n, int64_t padding_idx, double* out, int32_t* status,
+                             void* stream) {
+  return run_lookup<double>(table, height, d, ids, n, padding_idx, out, status, stream);
+}
+
+int b200emb_lookup_table_grad_sparse_f32(const int64_t* ids, const float* d_out, int64_t n,
+                                         int64_t d, int64_t* rows, float* value, void* stream) {
+  return run_grad_sparse<float>(ids, d_out, n, d, rows, value, stream);
+}
+int b200emb_lookup_table_grad_sparse_f64(const int64_t* ids, const double* d_out, int64_t n,
+                                         int64_t d, int64_t* rows, double* value, void* stream) {
+  return run_grad_sparse<double>(ids, d_out, n, d, rows, value, stream);
+}
+
+int b200emb_selected_rows_add_to(const int64_t* in_rows, const void* in_value, int64_t n_in,
+                                 int64_t d, int64_t elem_size, int64_t* out_rows,
+                                 void* out_value, int64_t row_offset, void* stream) {
+  if (n_in < 0 || d <= 0 || row_offset < 0 || elem_size <= 0) return B200EMB_E_INVALID;
+  if (n_in == 0) return B200EMB_OK;  // empty inputs are skipped (sum_op.h:129-131)
+  if (!in_rows || !in_value || !out_rows || !out_value) return B200EMB_E_INVALID;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  cudaError_t e = cudaMemcpyAsync(out_rows + row_offset, in_rows, sizeof(int64_t) * n_in,
+                                  cudaMemcpyDeviceToDevice, s);
+  if (e == cudaSuccess)
+    e = cudaMemcpyAsync(static_cast<char*>(out_value) + row_offset * d * elem_size, in_value,
+                        static_cast<size_t>(n_in) * d * elem_size, cudaMemcpyDeviceToDevice, s);
+  return e == cudaSuccess ? B200EMB_OK : fail_cuda(e);
+}
+
+int b200emb_plan_rows(const int64_t* rows, int64_t n, int64_t height, void* workspace,
+                      size_t workspace_bytes, int32_t* status, void* stream) {
+  int rc = check_sizes(n, 1, height);
+  if (rc != B200EMB_OK) return rc;
+  if (n == 0) return B200EMB_OK;
+  if (!rows) return B200EMB_E_INVALID;
+  // the plan region does not depend on d / elem_size; only the carry tail does
+  const Workspace L = make_workspace(n, 1, 4);
+  rc = check_workspace(workspace, workspace_bytes, L);
+  if (rc != B200EMB_OK) return rc;
+  cudaError_t e = launch_plan(rows, n, height, static_cast<char*>(workspace), L, status,
+                              static_cast<cudaStream_t>(stream), nullptr);
+  return e == cudaSuccess ? B200EMB_OK : fail_cuda(e);
+}
+
+#define B200EMB_DEFINE_UPDATES(T, S)                                                             \
+  int b200emb_merge_add_##S(const int64_t* rows, const T* value, int64_t n, int64_t d,           \
+                            int64_t height, int64_t* out_rows, T* out_value, int64_t* n_unique,  \
+                            void* workspace, size_t workspace_bytes, unsigned flags,             \
+                            int32_t* status, void* stream) {                                     \
+    UpdateArgs<T> a;                                                                             \
+    a.op = UpdateOp::kMergeAdd;                                                                  \
+    a.param = out_value;                                                                         \
+    return run_update<T>(rows, value, n, d, height, a, out_rows, n_unique, workspace,            \
+                         workspace_bytes, flags, status, stream, out_rows && n_unique);          \
+  }                                                                                              \
+  int b200emb_selected_rows_add_to_tensor_##S(const int64_t* rows, const T* value, int64_t n,    \
+                                              int64_t d, int64_t height, T* tensor,              \
+                                              void* workspace, size_t workspace_bytes,           \
+                                              unsigned flags, int32_t* status, void* stream) {   \
+    UpdateArgs<T> a;                                                                             \
+    a.op = UpdateOp::kAddToTensor;                                                               \
+    a.param = tensor;                                                                            \
+    return run_update<T>(rows, value, n, d, height, a, nullptr, nullptr, workspace,              \
+                         workspace_bytes, flags, status, stream, true);                          \
+  }                                                                                              \
+  int b200emb_sparse_sgd_##S(T* param, int64_t height, int64_t d, const int64_t* rows,           \
+                             const T* grad, int64_t n, const T* lr, void* workspace,             \
+                             size_t workspace_bytes, unsigned flags, int32_t* status,            \
+                             void* stream) {                                                     \
+    UpdateArgs<T> a;                                                                             \
+    a.op = UpdateOp::kSgd;                                                                       \
+    a.param = param;                                                                             \
+    a.lr = lr;                                                                                   \
+    return run_update<T>(rows, grad, n, d, height, a, nullptr, nullptr, workspace,               \
+                         workspace_bytes, flags, status, stream, lr != nullptr);                 \
+  }                                                                                              \
+  int b200emb_sparse_adam_##S(T* param, T* moment1, T* moment2, int64_t height, int64_t d,       \
+                              const int64_t* rows, const T* grad, int64_t n, const T* lr,        \
+                              const T* beta1_pow, const T* beta2_pow, float beta1, float beta2,  \
+                              float epsilon, void* workspace, size_t workspace_bytes,            \
+                              unsigned flags, int32_t* status, void* stream) {                   \
+    UpdateArgs<T> a;                                                                             \
+    a.op = UpdateOp::kAdam;                                                                      \
+    a.param = param;                                                                             \
+    a.moment1 = moment1;                                                                         \
+    a.moment2 = moment2;                                                                         \
+    a.lr = lr;                                                                                   \
+    a.beta1_pow = beta1_pow;                                                                     \
+    a.beta2_pow = beta2_pow;                                                                     \
+    a.beta1 = static_cast<T>(beta1);                                                             \
+    a.beta2 = static_cast<T>(beta2);                                                             \
+    a.epsilon = static_cast<T>(epsilon);                                                         \
+    return run_update<T>(rows, grad, n, d, height, a, nullptr, nullptr, workspace,               \
+                         workspace_bytes, flags, status, stream,                                 \
+                         lr && beta1_pow && beta2_pow && moment1 && moment2);                    \
+  }
+
+B200EMB_DEFINE_UPDATES(float, f32)
+B200EMB_DEFINE_UPDATES(double, f64)
+
+}  // extern "C"

@@ -1,0 +1,115 @@
+// common.cuh — shared device helpers for the sm_100a sparse-embedding kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200emb {
+
+constexpr uint32_t kNoKey = 0xFFFFFFFFu;  // never a valid sort key (height < 2^32-1)
+constexpr int kBlock = 256;               // threads per CTA for the row kernels
+
+// ---------------------------------------------------------------------------
+// IEEE round-to-nearest arithmetic that the compiler may not contract into FMAs: the
+// reference CPU build has no FMA (cmake/simd.cmake:11), so parity needs separate roundings.
+template <typename T> struct Arith;
+template <> struct Arith<float> {
+  static __device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
+  static __device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
+  static __device__ __forceinline__ float mul(float a, float b) { return __fmul_rn(a, b); }
+  static __device__ __forceinline__ float div(float a, float b) { return __fdiv_rn(a, b); }
+  static __device__ __forceinline__ float sqrt(float a) { return __fsqrt_rn(a); }
+};
+template <> struct Arith<double> {
+  static __device__ __forceinline__ double add(double a, double b) { return __dadd_rn(a, b); }
+  static __device__ __forceinline__ double sub(double a, double b) { return __dsub_rn(a, b); }
+  static __device__ __forceinline__ double mul(double a, double b) { return __dmul_rn(a, b); }
+  static __device__ __forceinline__ double div(double a, double b) { return __ddiv_rn(a, b); }
+  static __device__ __forceinline__ double sqrt(double a) { return __dsqrt_rn(a); }
+};
+
+// ---------------------------------------------------------------------------
+// A row of D elements is spread over a "group" of LPR lanes; each lane owns NV vectors of
+// EPV elements (16-byte vectors when VEC, single elements otherwise):
+//   column(l, k) = col0 + (l + k*LPR) * EPV,   k < NV.
+// A pass covers LPR*NV*EPV columns; wider rows loop over col0.
+template <typename T, bool VEC> struct Epv { static constexpr int value = VEC ? int(16 / sizeof(T)) : 1; };
+
+template <typename T, int EPV> struct Pack { T v[EPV]; };
+
+template <typename T, bool VEC>
+__device__ __forceinline__ void load_vec(const T* __restrict__ p, T (&dst)[Epv<T, VEC>::value]) {
+  if constexpr (VEC) {
+    const int4 raw = *reinterpret_cast<const int4*>(p);
+    *reinterpret_cast<int4*>(dst) = raw;
+  } else {
+    dst[0] = *p;
+  }
+}
+// streaming read of data touched once (gradient rows): bypass L1 allocation
+template <typename T, bool VEC>
+__device__ __forceinline__ void load_vec_stream(const T* __restrict__ p, T (&dst)[Epv<T, VEC>::value]) {
+  if constexpr (VEC) {
+    int4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    *reinterpret_cast<int4*>(dst) = r;
+  } else {
+    dst[0] = __ldg(p);
+  }
+}
+template <typename T, bool VEC>
+__device__ __forceinline__ void store_vec(T* p, const T (&src)[Epv<T, VEC>::value]) {
+  if constexpr (VEC) {
+    *reinterpret_cast<int4*>(p) = *reinterpret_cast<const int4*>(src);
+  } else {
+    *p = src[0];
+  }
+}
+template <typename T, bool VEC>
+__device__ __forceinline__ void store_vec_stream(T* p, const T (&src)[Epv<T, VEC>::value]) {
+  if constexpr (VEC) {
+    const int4 r = *reinterpret_cast<const int4*>(src);
+    asm volatile("st.global.L1::no_allocate.v4.s32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "r"(r.x), "r"(r.y), "r"(r.z), "r"(r.w) : "memory");
+  } else {
+    *p = src[0];
+  }
+}
+
+__device__ __forceinline__ uint32_t ld_relaxed(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t lanemask_lt() {
+  uint32_t m;
+  asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+  return m;
+}
+
+// ---------------------------------------------------------------------------
+// Row-shape dispatch: picks (LPR, NV, VEC) from D and pointer alignment and calls
+// f.template operator()<LPR, NV, VEC>().
+template <typename T, class F>
+inline void dispatch_row_shape(int64_t d, bool aligned16, F&& f) {
+  constexpr int epv = int(16 / sizeof(T));
+  if (aligned16 && d % epv == 0) {
+    const int64_t vecs = d / epv;
+    if (vecs <= 8) f.template operator()<8, 1, true>();
+    else if (vecs <= 16) f.template operator()<16, 1, true>();
+    else if (vecs <= 32) f.template operator()<32, 1, true>();
+    else if (vecs <= 64) f.template operator()<32, 2, true>();
+    else f.template operator()<32, 4, true>();
+  } else {
+    if (d <= 8) f.template operator()<8, 1, false>();
+    else if (d <= 16) f.template operator()<16, 1, false>();
+    else f.template operator()<32, 1, false>();
+  }
+}
+
+inline bool is_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+}  // namespace b200emb

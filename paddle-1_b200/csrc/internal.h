@@ -1,0 +1,96 @@
+// internal.h — host-side contracts between capi.cu and the kernel translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+namespace b200emb {
+
+// ---- radix sort geometry (sort.cu) -----------------------------------------------------
+constexpr int kRadixBits = 8;
+constexpr int kRadix = 1 << kRadixBits;
+constexpr int kSortThreads = 256;
+constexpr int kSortItems = 8;
+constexpr int kSortTile = kSortThreads * kSortItems;   // 2048 keys per tile
+constexpr int kMaxPasses = 4;                          // keys < 2^32
+constexpr int kScanTile = 2048;                        // head-flag scan tile
+
+// ---- segmented-reduce geometry (segreduce.cu) ------------------------------------------
+constexpr int kMinChunk = 4;     // sorted elements walked by one lane group, lower bound
+constexpr int kMaxChunk = 64;
+constexpr int kMinGroupsPerCta = 8;   // 256 threads / 32 lanes
+
+inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+
+// Everything the kernels keep in the caller's workspace.  Offsets in bytes.
+struct Workspace {
+  // zeroed at the start of every plan
+  size_t off_hist;        // u32 [kMaxPasses][kRadix]   global digit histograms
+  size_t off_tickets;     // u32 [8]                    dynamic tile counters (4 sort passes, 1 scan)
+  size_t off_lookback;    // u32 [kMaxPasses][sort_tiles][kRadix]
+  size_t off_scan_state;  // u32 [scan_tiles]
+  size_t zero_bytes;      // bytes [0, zero_bytes) are cleared by cudaMemsetAsync
+  // plan
+  size_t off_plan;        // PlanHeader
+  size_t off_keys[2];     // u32 [n]
+  size_t off_perm[2];     // u32 [n]
+  size_t off_uidx;        // u32 [n]   unique index of each sorted position
+  size_t off_seg_start;   // u32 [n+1] first sorted position of each unique row
+  // carries of the chunked reduce
+  size_t off_cta_flags;   // u32 [max_ctas]
+  size_t off_cta_tail_key;   // u32 [max_ctas]
+  size_t off_cta_tail_eref;  // u32 [max_ctas]
+  size_t off_cta_head;    // T [max_ctas][d]
+  size_t off_cta_tail;    // T [max_ctas][d]
+  size_t total;
+  int64_t sort_tiles, scan_tiles, max_ctas;
+};
+
+struct PlanHeader {      // lives in the workspace (device)
+  unsigned long long n_unique;  // written by the head scan
+};
+
+Workspace make_workspace(int64_t n, int64_t d, int64_t elem_size);
+
+struct SortedPlan {      // device pointers into the workspace after plan_rows
+  const uint32_t* keys;  // sorted ids (invalid ids -> `height`)
+  const uint32_t* perm;  // original position of each sorted element (stable)
+  int passes;
+};
+
+// sort.cu
+cudaError_t launch_plan(const int64_t* rows, int64_t n, int64_t height, char* ws,
+                        const Workspace& L, int32_t* status, cudaStream_t s, SortedPlan* out);
+SortedPlan plan_view(int64_t height, char* ws, const Workspace& L);
+cudaError_t launch_head_scan(const SortedPlan& plan, int64_t n, uint32_t invalid_key, char* ws,
+                             const Workspace& L, int64_t* out_rows, int64_t* n_unique_out,
+                             cudaStream_t s);
+
+// gather.cu
+template <typename T>
+cudaError_t launch_gather(const T* table, int64_t height, int64_t d, const int64_t* ids, int64_t n,
+                          int64_t padding_idx, T* out, int32_t* status, cudaStream_t s);
+
+// segreduce.cu
+enum class UpdateOp { kMergeAdd, kAddToTensor, kSgd, kAdam };
+template <typename T>
+struct UpdateArgs {
+  UpdateOp op;
+  T* param = nullptr;        // kSgd/kAdam: Param; kAddToTensor: the dense tensor; kMergeAdd: out_value
+  T* moment1 = nullptr;
+  T* moment2 = nullptr;
+  const T* lr = nullptr;
+  const T* beta1_pow = nullptr;
+  const T* beta2_pow = nullptr;
+  T beta1 = 0, beta2 = 0, epsilon = 0;
+  const uint32_t* uidx = nullptr;  // kMergeAdd: sorted position -> output row
+};
+template <typename T>
+cudaError_t launch_update(const SortedPlan& plan, const T* value, int64_t n, int64_t d,
+                          int64_t height, const UpdateArgs<T>& args, bool deterministic, char* ws,
+                          const Workspace& L, int32_t* status, cudaStream_t s);
+
+int choose_chunk(int64_t n, int groups_per_cta);
+
+}  // namespace b200emb

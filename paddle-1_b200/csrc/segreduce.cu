@@ -1,0 +1,483 @@
+// segreduce.cu — duplicate-row reduction fused with the consumer (K3/K4/K5a/K5b), sm_100a.
+//
+// Input: the sort plan (sorted ids + original positions) and the [N,D] gradient rows.
+// One skeleton, four consumers selected at compile time:
+//   kMergeAdd     out_value[u,:]  = sum           scatter::MergeAdd (selected_rows_functor.cc:193-228)
+//   kAddToTensor  tensor[id,:]   += sum           SelectedRowsAddToTensor (:153-178)
+//   kSgd          param[id,:]    -= lr*sum        sparse SGD (sgd_op.h:47-81)
+//   kAdam         lazy Adam on (param,m1,m2)[id]  SparseAdamFunctor (adam_op.h:199-219)
+// so merged gradient rows never travel through HBM: each input row is read once, each touched
+// parameter row is read and written once.
+//
+// FAST mode (k_chunk_reduce + k_fixup): the sorted element range is cut into equal chunks, one
+// per lane group, so work is balanced no matter how skewed the ids are (a Zipf head id owns
+// 10-25% of all rows).  A group walks its chunk with kBatch independent row loads in flight;
+// segments that close inside the chunk are consumed immediately.  Segments cut by a chunk
+// boundary leave partial sums in shared memory, are combined across the CTA's groups in fixed
+// order, and — if they also cross the CTA boundary — leave one carry row per CTA for k_fixup.
+// No atomics anywhere: the summation tree is fixed by (N, D) alone, hence run-to-run
+// deterministic.
+//
+// DETERMINISTIC mode (k_segment_det): one lane group per unique row walks its duplicates in input
+// order (the stable sort keeps it) with separately rounded IEEE operations, reproducing the
+// reference CPU loops bit for bit.  Its critical path is the longest duplicate run; it is the
+// parity mode, not the speed mode.
+#include <algorithm>
+
+#include "common.cuh"
+#include "internal.h"
+
+namespace b200emb {
+namespace {
+
+constexpr int kBatch = 4;
+constexpr uint32_t kHead = 1u, kTail = 2u, kThrough = 4u;             // per-group flags
+constexpr uint32_t kCtaHead = 1u, kCtaHeadThrough = 2u, kCtaTail = 4u;  // per-CTA flags
+
+template <typename T>
+struct Params {
+  T* param; T* m1; T* m2;
+  const T* lr; const T* b1p; const T* b2p;
+  T beta1, beta2, eps;
+  const uint32_t* uidx;
+  int d;
+  uint32_t height;
+};
+
+template <typename T>
+struct Carry {
+  uint32_t* flags; uint32_t* tail_key; uint32_t* tail_eref;
+  T* head; T* tail;
+};
+
+template <typename T, int NV, int EPV>
+__device__ __forceinline__ void zero_acc(T (&a)[NV][EPV]) {
+#pragma unroll
+  for (int k = 0; k < NV; ++k)
+#pragma unroll
+    for (int e = 0; e < EPV; ++e) a[k][e] = T(0);
+}
+
+// Consume one fully reduced row.  `eref` = any sorted position inside the segment.
+template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
+__device__ __forceinline__ void consume(const Params<T>& P, uint32_t key, uint32_t eref, int col0,
+                                        int l, const T (&acc)[NV][Epv<T, VEC>::value]) {
+  constexpr int EPV = Epv<T, VEC>::value;
+  using A = Arith<T>;
+  if (key >= P.height) return;  // out-of-range row: flagged by k_prepare, skipped here
+  const int64_t row = (OP == UpdateOp::kMergeAdd) ? static_cast<int64_t>(P.uidx[eref])
+                                                  : static_cast<int64_t>(key);
+  const int64_t base = row * P.d;
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    const int col = col0 + (l + k * LPR) * EPV;
+    if (col >= P.d) continue;
+    if constexpr (OP == UpdateOp::kMergeAdd) {
+      store_vec<T, VEC>(P.param + base + col, acc[k]);
+    } else if constexpr (OP == UpdateOp::kAddToTensor) {
+      T t[EPV];
+      load_vec<T, VEC>(P.param + base + col, t);
+#pragma unroll
+      for (int e = 0; e < EPV; ++e) t[e] = A::add(t[e], acc[k][e]);
+      store_vec<T, VEC>(P.param + base + col, t);
+    } else if constexpr (OP == UpdateOp::kSgd) {
+      T p[EPV];
+      load_vec<T, VEC>(P.param + base + col, p);
+      const T lr = *P.lr;
+#pragma unroll
+      for (int e = 0; e < EPV; ++e) p[e] = A::sub(p[e], A::mul(lr, acc[k][e]));
+      store_vec<T, VEC>(P.param + base + col, p);
+    } else {  // kAdam — operation order of adam_op.h:209-213, every step rounded in T
+      T p[EPV], m1[EPV], m2[EPV];
+      load_vec<T, VEC>(P.param + base + col, p);
+      load_vec<T, VEC>(P.m1 + base + col, m1);
+      load_vec<T, VEC>(P.m2 + base + col, m2);
+      const T one = T(1);
+      const T lr_t = A::mul(*P.lr, A::div(A::sqrt(A::sub(one, *P.b2p)), A::sub(one, *P.b1p)));
+      const T omb1 = A::sub(one, P.beta1), omb2 = A::sub(one, P.beta2);
+#pragma unroll
+      for (int e = 0; e < EPV; ++e) {
+        const T g = acc[k][e];
+        m1[e] = A::add(A::mul(P.beta1, m1[e]), A::mul(omb1, g));
+        m2[e] = A::add(A::mul(P.beta2, m2[e]), A::mul(A::mul(omb2, g), g));
+        p[e] = A::sub(p[e], A::mul(lr_t, A::div(m1[e], A::add(A::sqrt(m2[e]), P.eps))));
+      }
+      store_vec<T, VEC>(P.m1 + base + col, m1);
+      store_vec<T, VEC>(P.m2 + base + col, m2);
+      store_vec<T, VEC>(P.param + base + col, p);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
+__global__ void __launch_bounds__(kBlock)
+k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ perm, int n,
+               int chunk, const T* __restrict__ value, Params<T> P, Carry<T> C) {
+  constexpr int EPV = Epv<T, VEC>::value;
+  constexpr int GPC = kBlock / LPR;
+  constexpr int COLS = LPR * NV * EPV;
+  using A = Arith<T>;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  T* s_head = reinterpret_cast<T*>(smem_raw);                 // [GPC][COLS]
+  T* s_tail = s_head + GPC * COLS;                            // [GPC][COLS]
+  uint32_t* s_key = reinterpret_cast<uint32_t*>(s_tail + GPC * COLS);  // [GPC*chunk]
+  uint32_t* s_perm = s_key + GPC * chunk;
+  __shared__ uint32_t s_flags[GPC];
+  __shared__ uint32_t s_prev_key, s_next_key, s_cta_flags;
+
+  const int tid = threadIdx.x, g = tid / LPR, l = tid % LPR;
+  const int d = P.d;
+  const int cta_start = blockIdx.x * GPC * chunk;
+  const int cta_count = min(GPC * chunk, n - cta_start);
+  for (int i = tid; i < cta_count; i += kBlock) {
+    s_key[i] = skey[cta_start + i];
+    s_perm[i] = perm[cta_start + i];
+  }
+  if (tid == 0) {
+    s_prev_key = cta_start > 0 ? skey[cta_start - 1] : kNoKey;
+    s_next_key = cta_start + cta_count < n ? skey[cta_start + cta_count] : kNoKey;
+    s_cta_flags = 0;
+  }
+  __syncthreads();
+
+  const int gs = g * chunk;
+  const int ge = min(gs + chunk, cta_count);
+  const bool active = gs < cta_count;
+
+  for (int col0 = 0; col0 < d; col0 += COLS) {
+    uint32_t flags = 0, tail_key = 0, tail_eref = 0;
+    if (active) {
+      const uint32_t prev = gs > 0 ? s_key[gs - 1] : s_prev_key;
+      const uint32_t next = ge < cta_count ? s_key[ge] : s_next_key;
+      uint32_t cur = s_key[gs];
+      bool first = true;
+      T acc[NV][EPV];
+      zero_acc<T, NV, EPV>(acc);
+
+      auto flush = [&](bool right_open, int e_last) {
+        const bool left_open = first && cur == prev;
+        if (!left_open && !right_open) {
+          consume<T, OP, LPR, NV, VEC>(P, cur, static_cast<uint32_t>(cta_start + e_last), col0, l, acc);
+        } else {
+          T* dst = (left_open ? s_head : s_tail) + g * COLS;
+#pragma unroll
+          for (int k = 0; k < NV; ++k)
+#pragma unroll
+            for (int e = 0; e < EPV; ++e) dst[(l + k * LPR) * EPV + e] = acc[k][e];
+          if (left_open) {
+            flags |= kHead | (right_open ? kThrough : 0u);
+          } else {
+            flags |= kTail;
+            tail_key = cur;
+            tail_eref = static_cast<uint32_t>(cta_start + e_last);
+          }
+        }
+      };
+
+      for (int e0 = gs; e0 < ge; e0 += kBatch) {
+        uint32_t k[kBatch];
+        T r[kBatch][NV][EPV];
+#pragma unroll
+        for (int b = 0; b < kBatch; ++b) {
+          const int idx = e0 + b;
+          const bool in = idx < ge;
+          k[b] = in ? s_key[idx] : cur;
+          const int64_t src = in ? static_cast<int64_t>(s_perm[idx]) * d : 0;
+#pragma unroll
+          for (int kk = 0; kk < NV; ++kk) {
+            const int col = col0 + (l + kk * LPR) * EPV;
+            if (in && col < d) load_vec_stream<T, VEC>(value + src + col, r[b][kk]);
+            else {
+#pragma unroll
+              for (int e = 0; e < EPV; ++e) r[b][kk][e] = T(0);
+            }
+          }
+        }
+#pragma unroll
+        for (int b = 0; b < kBatch; ++b) {
+          if (e0 + b < ge) {
+            if (k[b] != cur) {
+              flush(false, e0 + b - 1);
+              zero_acc<T, NV, EPV>(acc);
+              cur = k[b];
+              first = false;
+            }
+#pragma unroll
+            for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+              for (int e = 0; e < EPV; ++e) acc[kk][e] = A::add(acc[kk][e], r[b][kk][e]);
+          }
+        }
+      }
+      flush(cur == next, ge - 1);
+    }
+    if (l == 0) s_flags[g] = flags;
+    __syncthreads();
+
+    // ---- combine partial segments across the CTA's groups, in group order -----------------
+    if (active && (flags & kTail)) {
+      T sum[NV][EPV];
+#pragma unroll
+      for (int k = 0; k < NV; ++k)
+#pragma unroll
+        for (int e = 0; e < EPV; ++e) sum[k][e] = s_tail[g * COLS + (l + k * LPR) * EPV + e];
+      int j = g + 1;
+      bool to_end = true;
+      while (j < GPC) {
+        const uint32_t f = s_flags[j];
+        if (!(f & kHead)) { to_end = false; break; }
+#pragma unroll
+        for (int k = 0; k < NV; ++k)
+#pragma unroll
+          for (int e = 0; e < EPV; ++e)
+            sum[k][e] = A::add(sum[k][e], s_head[j * COLS + (l + k * LPR) * EPV + e]);
+        if (!(f & kThrough)) { to_end = false; break; }
+        ++j;
+      }
+      if (to_end) {  // the segment runs past the CTA's last element: leave a carry
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+          const int col = col0 + (l + k * LPR) * EPV;
+          if (col < d) store_vec<T, VEC>(C.tail + static_cast<int64_t>(blockIdx.x) * d + col, sum[k]);
+        }
+        if (l == 0) {
+          C.tail_key[blockIdx.x] = tail_key;
+          C.tail_eref[blockIdx.x] = tail_eref;
+          atomicOr(&s_cta_flags, kCtaTail);
+        }
+      } else {
+        consume<T, OP, LPR, NV, VEC>(P, tail_key, tail_eref, col0, l, sum);
+      }
+    }
+    if (g == 0 && active && (flags & kHead)) {  // segment entering from the previous CTA
+      T sum[NV][EPV];
+#pragma unroll
+      for (int k = 0; k < NV; ++k)
+#pragma unroll
+        for (int e = 0; e < EPV; ++e) sum[k][e] = s_head[(l + k * LPR) * EPV + e];
+      bool to_end = (flags & kThrough) != 0;
+      int j = 1;
+      while (to_end && j < GPC) {
+        const uint32_t f = s_flags[j];
+        if (!(f & kHead)) { to_end = false; break; }
+#pragma unroll
+        for (int k = 0; k < NV; ++k)
+#pragma unroll
+          for (int e = 0; e < EPV; ++e)
+            sum[k][e] = A::add(sum[k][e], s_head[j * COLS + (l + k * LPR) * EPV + e]);
+        if (!(f & kThrough)) { to_end = false; break; }
+        ++j;
+      }
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        const int col = col0 + (l + k * LPR) * EPV;
+        if (col < d) store_vec<T, VEC>(C.head + static_cast<int64_t>(blockIdx.x) * d + col, sum[k]);
+      }
+      if (l == 0) atomicOr(&s_cta_flags, kCtaHead | (to_end ? kCtaHeadThrough : 0u));
+    }
+    __syncthreads();
+  }
+  if (tid == 0) C.flags[blockIdx.x] = s_cta_flags;
+}
+
+// One lane group per CTA-boundary carry: tail of CTA c + heads of the following CTAs.
+template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
+__global__ void __launch_bounds__(kBlock)
+k_fixup(int num_ctas, Params<T> P, Carry<T> C) {
+  constexpr int EPV = Epv<T, VEC>::value;
+  constexpr int GPC = kBlock / LPR;
+  constexpr int COLS = LPR * NV * EPV;
+  using A = Arith<T>;
+  const int l = threadIdx.x % LPR;
+  const int d = P.d;
+  for (int c = blockIdx.x * GPC + threadIdx.x / LPR; c < num_ctas; c += gridDim.x * GPC) {
+    if (!(C.flags[c] & kCtaTail)) continue;
+    const uint32_t key = C.tail_key[c], eref = C.tail_eref[c];
+    for (int col0 = 0; col0 < d; col0 += COLS) {
+      T sum[NV][EPV];
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        const int col = col0 + (l + k * LPR) * EPV;
+        if (col < d) load_vec<T, VEC>(C.tail + static_cast<int64_t>(c) * d + col, sum[k]);
+        else {
+#pragma unroll
+          for (int e = 0; e < EPV; ++e) sum[k][e] = T(0);
+        }
+      }
+      for (int j = c + 1; j < num_ctas; ++j) {
+        const uint32_t f = C.flags[j];
+        if (!(f & kCtaHead)) break;
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+          const int col = col0 + (l + k * LPR) * EPV;
+          if (col < d) {
+            T h[EPV];
+            load_vec<T, VEC>(C.head + static_cast<int64_t>(j) * d + col, h);
+#pragma unroll
+            for (int e = 0; e < EPV; ++e) sum[k][e] = A::add(sum[k][e], h[e]);
+          }
+        }
+        if (!(f & kCtaHeadThrough)) break;
+      }
+      consume<T, OP, LPR, NV, VEC>(P, key, eref, col0, l, sum);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Bit-exact order mode: one lane group per unique row, duplicates in input order.
+template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
+__global__ void __launch_bounds__(kBlock)
+k_segment_det(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ perm, int n,
+              const uint32_t* __restrict__ seg_start, const PlanHeader* hdr,
+              const T* __restrict__ value, Params<T> P) {
+  constexpr int EPV = Epv<T, VEC>::value;
+  constexpr int GPC = kBlock / LPR;
+  constexpr int COLS = LPR * NV * EPV;
+  constexpr int kPrefetch = NV >= 4 ? 2 : (NV == 2 ? 4 : 8);
+  using A = Arith<T>;
+  const int l = threadIdx.x % LPR;
+  const int d = P.d;
+  const int n_unique = static_cast<int>(hdr->n_unique);
+  for (int s = blockIdx.x * GPC + threadIdx.x / LPR; s < n_unique; s += gridDim.x * GPC) {
+    const int b = static_cast<int>(seg_start[s]);
+    const uint32_t key = skey[b];
+    for (int col0 = 0; col0 < d; col0 += COLS) {
+      T acc[NV][EPV];
+      if constexpr (OP == UpdateOp::kSgd || OP == UpdateOp::kAddToTensor) {
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+          const int col = col0 + (l + k * LPR) * EPV;
+          if (col < d) load_vec<T, VEC>(P.param + static_cast<int64_t>(key) * d + col, acc[k]);
+          else {
+#pragma unroll
+            for (int e = 0; e < EPV; ++e) acc[k][e] = T(0);
+          }
+        }
+      } else {
+        zero_acc<T, NV, EPV>(acc);  // MergeAdd starts from +0.0 (SetConstant, selected_rows_functor.cc:211-212)
+      }
+      T lr = T(0);
+      if constexpr (OP == UpdateOp::kSgd) lr = *P.lr;
+      bool more = true;
+      for (int e0 = b; more; e0 += kPrefetch) {
+        T r[kPrefetch][NV][EPV];
+        bool same[kPrefetch];
+#pragma unroll
+        for (int q = 0; q < kPrefetch; ++q) {
+          const int idx = e0 + q;
+          same[q] = idx < n && skey[idx] == key;
+          const int64_t src = same[q] ? static_cast<int64_t>(perm[idx]) * d : 0;
+#pragma unroll
+          for (int k = 0; k < NV; ++k) {
+            const int col = col0 + (l + k * LPR) * EPV;
+            if (same[q] && col < d) load_vec_stream<T, VEC>(value + src + col, r[q][k]);
+            else {
+#pragma unroll
+              for (int e = 0; e < EPV; ++e) r[q][k][e] = T(0);
+            }
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < kPrefetch; ++q) {
+          if (more && same[q]) {
+#pragma unroll
+            for (int k = 0; k < NV; ++k)
+#pragma unroll
+              for (int e = 0; e < EPV; ++e) {
+                if constexpr (OP == UpdateOp::kSgd)
+                  acc[k][e] = A::sub(acc[k][e], A::mul(lr, r[q][k][e]));  // sgd_op.h:77-79
+                else
+                  acc[k][e] = A::add(acc[k][e], r[q][k][e]);
+              }
+          } else {
+            more = false;
+          }
+        }
+      }
+      if constexpr (OP == UpdateOp::kSgd || OP == UpdateOp::kAddToTensor) {
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+          const int col = col0 + (l + k * LPR) * EPV;
+          if (col < d) store_vec<T, VEC>(P.param + static_cast<int64_t>(key) * d + col, acc[k]);
+        }
+      } else {
+        consume<T, OP, LPR, NV, VEC>(P, key, static_cast<uint32_t>(b), col0, l, acc);
+      }
+    }
+  }
+}
+
+template <typename T, UpdateOp OP>
+cudaError_t launch_op(const SortedPlan& plan, const T* value, int64_t n, int64_t d, int64_t height,
+                      const UpdateArgs<T>& a, bool deterministic, char* ws, const Workspace& L,
+                      cudaStream_t s) {
+  Params<T> P{a.param, a.moment1, a.moment2, a.lr, a.beta1_pow, a.beta2_pow,
+              a.beta1, a.beta2, a.epsilon, a.uidx, static_cast<int>(d),
+              static_cast<uint32_t>(height)};
+  Carry<T> C{reinterpret_cast<uint32_t*>(ws + L.off_cta_flags),
+             reinterpret_cast<uint32_t*>(ws + L.off_cta_tail_key),
+             reinterpret_cast<uint32_t*>(ws + L.off_cta_tail_eref),
+             reinterpret_cast<T*>(ws + L.off_cta_head), reinterpret_cast<T*>(ws + L.off_cta_tail)};
+  bool aligned = is_aligned16(value) && is_aligned16(a.param);
+  if (OP == UpdateOp::kAdam) aligned = aligned && is_aligned16(a.moment1) && is_aligned16(a.moment2);
+  cudaError_t err = cudaSuccess;
+  const int ni = static_cast<int>(n);
+  dispatch_row_shape<T>(d, aligned, [&]<int LPR, int NV, bool VEC>() {
+    constexpr int GPC = kBlock / LPR;
+    constexpr int COLS = LPR * NV * Epv<T, VEC>::value;
+    if (deterministic) {
+      const int grid = static_cast<int>(std::min<int64_t>(ceil_div(n, GPC), 148 * 8));
+      k_segment_det<T, OP, LPR, NV, VEC><<<grid, kBlock, 0, s>>>(
+          plan.keys, plan.perm, ni, reinterpret_cast<const uint32_t*>(ws + L.off_seg_start),
+          reinterpret_cast<const PlanHeader*>(ws + L.off_plan), value, P);
+    } else {
+      const int chunk = choose_chunk(n, GPC);
+      const int ctas = static_cast<int>(ceil_div(n, static_cast<int64_t>(GPC) * chunk));
+      const size_t smem = sizeof(T) * 2 * GPC * COLS + sizeof(uint32_t) * 2 * GPC * chunk;
+      k_chunk_reduce<T, OP, LPR, NV, VEC><<<ctas, kBlock, smem, s>>>(plan.keys, plan.perm, ni, chunk,
+                                                                     value, P, C);
+      const int fgrid = static_cast<int>(std::min<int64_t>(ceil_div(ctas, GPC), 148 * 8));
+      k_fixup<T, OP, LPR, NV, VEC><<<fgrid, kBlock, 0, s>>>(ctas, P, C);
+    }
+    err = cudaGetLastError();
+  });
+  return err;
+}
+
+}  // namespace
+
+int choose_chunk(int64_t n, int groups_per_cta) {
+  // one full wave of lane groups across the chip (148 SMs x 8 CTAs), chunk clamped to [4, 64]
+  const int64_t target_groups = 148LL * 8 * groups_per_cta;
+  int64_t c = ceil_div(n, target_groups);
+  c = std::max<int64_t>(kMinChunk, std::min<int64_t>(kMaxChunk, c));
+  return static_cast<int>(c);
+}
+
+template <typename T>
+cudaError_t launch_update(const SortedPlan& plan, const T* value, int64_t n, int64_t d,
+                          int64_t height, const UpdateArgs<T>& a, bool deterministic, char* ws,
+                          const Workspace& L, int32_t* /*status*/, cudaStream_t s) {
+  switch (a.op) {
+    case UpdateOp::kMergeAdd:
+      return launch_op<T, UpdateOp::kMergeAdd>(plan, value, n, d, height, a, deterministic, ws, L, s);
+    case UpdateOp::kAddToTensor:
+      return launch_op<T, UpdateOp::kAddToTensor>(plan, value, n, d, height, a, deterministic, ws, L, s);
+    case UpdateOp::kSgd:
+      return launch_op<T, UpdateOp::kSgd>(plan, value, n, d, height, a, deterministic, ws, L, s);
+    case UpdateOp::kAdam:
+      return launch_op<T, UpdateOp::kAdam>(plan, value, n, d, height, a, deterministic, ws, L, s);
+  }
+  return cudaErrorInvalidValue;
+}
+
+template cudaError_t launch_update<float>(const SortedPlan&, const float*, int64_t, int64_t, int64_t,
+                                          const UpdateArgs<float>&, bool, char*, const Workspace&,
+                                          int32_t*, cudaStream_t);
+template cudaError_t launch_update<double>(const SortedPlan&, const double*, int64_t, int64_t,
+                                           int64_t, const UpdateArgs<double>&, bool, char*,
+                                           const Workspace&, int32_t*, cudaStream_t);
+
+}  // namespace b200emb
