@@ -80,6 +80,21 @@ def _need_cuda(*tensors):
             raise B200EmbError("b200emb ops need contiguous tensors")
 
 
+def radix_passes(height):
+    """Number of 8-bit radix passes the sort plan runs for ids in [0, height] (sort.cu key_bits)."""
+    bits = 1
+    while (1 << bits) <= int(height):
+        bits += 1
+    return (bits + 7) // 8
+
+
+def plan_kernel_count(n, height):
+    """Kernels one sort plan launches: 1 (cluster sort, n <= 16*8704) else prepare + radix passes."""
+    if 0 < n <= 16 * 8704 and "B200EMB_FORCE_GLOBAL_SORT" not in os.environ:
+        return 1
+    return 1 + radix_passes(height)
+
+
 def workspace_bytes(n, d, elem_size=4):
     return int(lib().b200emb_workspace_bytes(int(n), int(d), int(elem_size)))
 

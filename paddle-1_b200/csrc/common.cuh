@@ -90,6 +90,21 @@ __device__ __forceinline__ uint32_t lanemask_lt() {
   return m;
 }
 
+// Lanes of the warp that hold the same BITS-bit digit (valid lanes only).  Built from BITS warp
+// ballots: the hardware MATCH.ANY instruction measured ~1 us per warp-instruction on sm_100a
+// (profiles/r1_notes.md), the ballot form is ~20 issue slots.
+template <int BITS>
+__device__ __forceinline__ uint32_t match_digit(uint32_t digit, bool valid) {
+  uint32_t peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+  for (int b = 0; b < BITS; ++b) {
+    const bool bit = (digit >> b) & 1u;
+    const uint32_t m = __ballot_sync(0xffffffffu, bit);
+    peers &= bit ? m : ~m;
+  }
+  return peers;
+}
+
 // ---------------------------------------------------------------------------
 // Row-shape dispatch: picks (LPR, NV, VEC) from D and pointer alignment and calls
 // f.template operator()<LPR, NV, VEC>().

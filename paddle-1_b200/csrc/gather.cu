@@ -16,7 +16,7 @@ namespace {
 constexpr int kRowsInFlight = 4;
 
 template <typename T, int LPR, int NV, bool VEC>
-__global__ void __launch_bounds__(kBlock)
+__global__ void __launch_bounds__(kBlock, 4)
 k_gather(const T* __restrict__ table, const int64_t* __restrict__ ids, T* __restrict__ out,
          int64_t n, int64_t height, int d, int64_t padding_idx, int32_t* status) {
   constexpr int EPV = Epv<T, VEC>::value;
@@ -25,18 +25,30 @@ k_gather(const T* __restrict__ table, const int64_t* __restrict__ ids, T* __rest
   const int64_t group = static_cast<int64_t>(blockIdx.x) * kGroups + threadIdx.x / LPR;
   const int64_t num_groups = static_cast<int64_t>(gridDim.x) * kGroups;
   bool bad = false;
-  for (int64_t base = group; base < n; base += num_groups * kRowsInFlight) {
+  const int64_t step = num_groups * kRowsInFlight;
+  int64_t nid[kRowsInFlight];   // ids of the batch after the current one (software prefetch)
+#pragma unroll
+  for (int r = 0; r < kRowsInFlight; ++r) {
+    const int64_t k = group + r * num_groups;
+    nid[r] = k < n ? ids[k] : 0;
+  }
+  for (int64_t base = group; base < n; base += step) {
     int64_t id[kRowsInFlight];
     bool live[kRowsInFlight], copy[kRowsInFlight];
 #pragma unroll
     for (int r = 0; r < kRowsInFlight; ++r) {
       const int64_t k = base + r * num_groups;
       live[r] = k < n;
-      id[r] = live[r] ? ids[k] : 0;
+      id[r] = nid[r];
       const bool pad = padding_idx != -1 && id[r] == padding_idx;   // lookup_table_op.h:56
       const bool ok = id[r] >= 0 && id[r] < height;                 // lookup_table_op.h:59-60
       copy[r] = live[r] && !pad && ok;
       bad |= live[r] && !pad && !ok;
+    }
+#pragma unroll
+    for (int r = 0; r < kRowsInFlight; ++r) {
+      const int64_t k = base + step + r * num_groups;
+      nid[r] = k < n ? ids[k] : 0;
     }
     for (int col0 = 0; col0 < d; col0 += LPR * NV * EPV) {
       T v[kRowsInFlight][NV][EPV];
@@ -75,8 +87,9 @@ cudaError_t launch_gather(const T* table, int64_t height, int64_t d, const int64
   cudaError_t err = cudaSuccess;
   dispatch_row_shape<T>(d, aligned, [&]<int LPR, int NV, bool VEC>() {
     constexpr int kGroups = kBlock / LPR;
+    // one resident wave (4 CTAs of 256 threads per SM leaves room for the concurrent sort cluster)
     const int64_t want = ceil_div(n, static_cast<int64_t>(kGroups));
-    const int grid = static_cast<int>(std::min<int64_t>(want, 148 * 8));
+    const int grid = static_cast<int>(std::min<int64_t>(want, 148 * 4));
     k_gather<T, LPR, NV, VEC><<<grid, kBlock, 0, s>>>(table, ids, out, n, height,
                                                       static_cast<int>(d), padding_idx, status);
     err = cudaGetLastError();

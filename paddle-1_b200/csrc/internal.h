@@ -67,6 +67,12 @@ cudaError_t launch_head_scan(const SortedPlan& plan, int64_t n, uint32_t invalid
                              const Workspace& L, int64_t* out_rows, int64_t* n_unique_out,
                              cudaStream_t s);
 
+// cluster_sort.cu
+bool cluster_sort_fits(int64_t n);
+cudaError_t launch_cluster_sort(const int64_t* rows, int64_t n, int64_t height, int passes,
+                                uint32_t* keys_out, uint32_t* perm_out, int32_t* status,
+                                cudaStream_t s);
+
 // gather.cu
 template <typename T>
 cudaError_t launch_gather(const T* table, int64_t height, int64_t d, const int64_t* ids, int64_t n,
@@ -91,6 +97,6 @@ cudaError_t launch_update(const SortedPlan& plan, const T* value, int64_t n, int
                           int64_t height, const UpdateArgs<T>& args, bool deterministic, char* ws,
                           const Workspace& L, int32_t* status, cudaStream_t s);
 
-int choose_chunk(int64_t n, int groups_per_cta);
+int choose_chunk(int64_t n, int groups_per_sm);
 
 }  // namespace b200emb

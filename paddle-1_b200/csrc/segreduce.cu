@@ -30,7 +30,6 @@
 namespace b200emb {
 namespace {
 
-constexpr int kBatch = 4;
 constexpr uint32_t kHead = 1u, kTail = 2u, kThrough = 4u;             // per-group flags
 constexpr uint32_t kCtaHead = 1u, kCtaHeadThrough = 2u, kCtaTail = 4u;  // per-CTA flags
 
@@ -111,12 +110,13 @@ __device__ __forceinline__ void consume(const Params<T>& P, uint32_t key, uint32
 
 // ------------------------------------------------------------------------------------------
 template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
-__global__ void __launch_bounds__(kBlock)
+__global__ void __launch_bounds__(kBlock, 4)
 k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ perm, int n,
                int chunk, const T* __restrict__ value, Params<T> P, Carry<T> C) {
   constexpr int EPV = Epv<T, VEC>::value;
   constexpr int GPC = kBlock / LPR;
   constexpr int COLS = LPR * NV * EPV;
+  constexpr int kBatch = NV == 1 ? 8 : 4;  // independent gradient rows in flight per group
   using A = Arith<T>;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T* s_head = reinterpret_cast<T*>(smem_raw);                 // [GPC][COLS]
@@ -281,21 +281,60 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
   if (tid == 0) C.flags[blockIdx.x] = s_cta_flags;
 }
 
-// One lane group per CTA-boundary carry: tail of CTA c + heads of the following CTAs.
+// One CTA per chunk-CTA boundary.  A CTA whose predecessor kernel left a tail carry owns the
+// segment.  Round trip 1: every thread reads one following CTA's flag word (256 per sweep) and
+// warp ballots find the chain length L (how many following CTAs contributed a head).  Round
+// trip 2: the lane groups sum the L head rows, strided by group, with all loads in flight, and
+// group 0 adds the per-group partials to the tail in group order.  A hot id spanning hundreds
+// of CTAs therefore costs a few memory round trips instead of one per carry row.  CTAs without
+// a tail exit at once.
 template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
 __global__ void __launch_bounds__(kBlock)
 k_fixup(int num_ctas, Params<T> P, Carry<T> C) {
   constexpr int EPV = Epv<T, VEC>::value;
   constexpr int GPC = kBlock / LPR;
   constexpr int COLS = LPR * NV * EPV;
+  constexpr int kRows = NV == 1 ? 8 : 4;  // head rows in flight per group
+  constexpr int kWarps = kBlock / 32;
   using A = Arith<T>;
-  const int l = threadIdx.x % LPR;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  T* s_part = reinterpret_cast<T*>(smem_raw);  // [GPC][COLS]
+  __shared__ int s_stop[kWarps];               // per warp: first index where the chain ends, or -1
+  __shared__ int s_stop_has[kWarps];
+  const int c = blockIdx.x;
+  const int tid = threadIdx.x, g = tid / LPR, l = tid % LPR, lane = tid & 31, warp = tid >> 5;
   const int d = P.d;
-  for (int c = blockIdx.x * GPC + threadIdx.x / LPR; c < num_ctas; c += gridDim.x * GPC) {
-    if (!(C.flags[c] & kCtaTail)) continue;
-    const uint32_t key = C.tail_key[c], eref = C.tail_eref[c];
-    for (int col0 = 0; col0 < d; col0 += COLS) {
-      T sum[NV][EPV];
+  // own flag and the first sweep of followers are fetched together
+  const uint32_t own = C.flags[c];
+  int len = 0;
+  bool first = true;
+  for (int base = c + 1;; base += kBlock) {
+    const int j = base + tid;
+    const uint32_t f = j < num_ctas ? C.flags[j] : 0u;
+    if (first && !(own & kCtaTail)) return;
+    first = false;
+    const bool has = (f & kCtaHead) != 0;
+    const bool cont = has && (f & kCtaHeadThrough) != 0;
+    const uint32_t stop = __ballot_sync(0xffffffffu, !cont);
+    const int sl = stop ? __ffs(stop) - 1 : -1;
+    const int sl_has = __shfl_sync(0xffffffffu, has ? 1 : 0, sl < 0 ? 0 : sl);
+    if (lane == 0) {
+      s_stop[warp] = sl < 0 ? -1 : warp * 32 + sl;
+      s_stop_has[warp] = sl_has;
+    }
+    __syncthreads();
+    int found = -1, found_has = 0;
+#pragma unroll
+    for (int w = kWarps - 1; w >= 0; --w)
+      if (s_stop[w] >= 0) { found = s_stop[w]; found_has = s_stop_has[w]; }
+    __syncthreads();
+    if (found >= 0) { len += found + found_has; break; }
+    len += kBlock;
+  }
+  const uint32_t key = C.tail_key[c], eref = C.tail_eref[c];
+  for (int col0 = 0; col0 < d; col0 += COLS) {
+    T sum[NV][EPV];
+    if (g == 0) {  // tail row: issued before the head rows so the loads overlap
 #pragma unroll
       for (int k = 0; k < NV; ++k) {
         const int col = col0 + (l + k * LPR) * EPV;
@@ -305,23 +344,50 @@ k_fixup(int num_ctas, Params<T> P, Carry<T> C) {
           for (int e = 0; e < EPV; ++e) sum[k][e] = T(0);
         }
       }
-      for (int j = c + 1; j < num_ctas; ++j) {
-        const uint32_t f = C.flags[j];
-        if (!(f & kCtaHead)) break;
+    }
+    T part[NV][EPV];
+    zero_acc<T, NV, EPV>(part);
+    for (int r0 = g; r0 < len; r0 += GPC * kRows) {
+      T h[kRows][NV][EPV];
+#pragma unroll
+      for (int q = 0; q < kRows; ++q) {
+        const int r = r0 + q * GPC;
 #pragma unroll
         for (int k = 0; k < NV; ++k) {
           const int col = col0 + (l + k * LPR) * EPV;
-          if (col < d) {
-            T h[EPV];
-            load_vec<T, VEC>(C.head + static_cast<int64_t>(j) * d + col, h);
+          if (r < len && col < d)
+            load_vec<T, VEC>(C.head + static_cast<int64_t>(c + 1 + r) * d + col, h[q][k]);
+          else {
 #pragma unroll
-            for (int e = 0; e < EPV; ++e) sum[k][e] = A::add(sum[k][e], h[e]);
+            for (int e = 0; e < EPV; ++e) h[q][k][e] = T(0);
           }
         }
-        if (!(f & kCtaHeadThrough)) break;
       }
+#pragma unroll
+      for (int q = 0; q < kRows; ++q)
+        if (r0 + q * GPC < len) {
+#pragma unroll
+          for (int k = 0; k < NV; ++k)
+#pragma unroll
+            for (int e = 0; e < EPV; ++e) part[k][e] = A::add(part[k][e], h[q][k][e]);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < NV; ++k)
+#pragma unroll
+      for (int e = 0; e < EPV; ++e) s_part[g * COLS + (l + k * LPR) * EPV + e] = part[k][e];
+    __syncthreads();
+    if (g == 0) {
+      const int used = min(len, GPC);
+      for (int j = 0; j < used; ++j)
+#pragma unroll
+        for (int k = 0; k < NV; ++k)
+#pragma unroll
+          for (int e = 0; e < EPV; ++e)
+            sum[k][e] = A::add(sum[k][e], s_part[j * COLS + (l + k * LPR) * EPV + e]);
       consume<T, OP, LPR, NV, VEC>(P, key, eref, col0, l, sum);
     }
+    __syncthreads();
   }
 }
 
@@ -433,13 +499,23 @@ cudaError_t launch_op(const SortedPlan& plan, const T* value, int64_t n, int64_t
           plan.keys, plan.perm, ni, reinterpret_cast<const uint32_t*>(ws + L.off_seg_start),
           reinterpret_cast<const PlanHeader*>(ws + L.off_plan), value, P);
     } else {
-      const int chunk = choose_chunk(n, GPC);
+      // one wave: as many lane groups as the chip holds at this kernel's real occupancy
+      static thread_local int occ_cache = 0;
+      if (occ_cache == 0) {
+        int occ = 0;
+        const size_t probe = sizeof(T) * 2 * GPC * COLS + sizeof(uint32_t) * 2 * GPC * 16;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+                &occ, k_chunk_reduce<T, OP, LPR, NV, VEC>, kBlock, probe) != cudaSuccess || occ < 1)
+          occ = 4;
+        occ_cache = occ;
+      }
+      const int chunk = choose_chunk(n, GPC * occ_cache);
       const int ctas = static_cast<int>(ceil_div(n, static_cast<int64_t>(GPC) * chunk));
       const size_t smem = sizeof(T) * 2 * GPC * COLS + sizeof(uint32_t) * 2 * GPC * chunk;
       k_chunk_reduce<T, OP, LPR, NV, VEC><<<ctas, kBlock, smem, s>>>(plan.keys, plan.perm, ni, chunk,
                                                                      value, P, C);
-      const int fgrid = static_cast<int>(std::min<int64_t>(ceil_div(ctas, GPC), 148 * 8));
-      k_fixup<T, OP, LPR, NV, VEC><<<fgrid, kBlock, 0, s>>>(ctas, P, C);
+      if (ctas > 1)
+        k_fixup<T, OP, LPR, NV, VEC><<<ctas, kBlock, sizeof(T) * GPC * COLS, s>>>(ctas, P, C);
     }
     err = cudaGetLastError();
   });
@@ -448,9 +524,9 @@ cudaError_t launch_op(const SortedPlan& plan, const T* value, int64_t n, int64_t
 
 }  // namespace
 
-int choose_chunk(int64_t n, int groups_per_cta) {
-  // one full wave of lane groups across the chip (148 SMs x 8 CTAs), chunk clamped to [4, 64]
-  const int64_t target_groups = 148LL * 8 * groups_per_cta;
+int choose_chunk(int64_t n, int groups_per_sm) {
+  // one full wave of lane groups across the chip's 148 SMs, chunk clamped to [4, 64]
+  const int64_t target_groups = 148LL * groups_per_sm;
   int64_t c = ceil_div(n, target_groups);
   c = std::max<int64_t>(kMinChunk, std::min<int64_t>(kMaxChunk, c));
   return static_cast<int>(c);

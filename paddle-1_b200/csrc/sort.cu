@@ -14,6 +14,9 @@
 // Only ceil(log2(height+1)) key bits are sorted.  The sort moves 8 B per id per pass, which is
 // noise next to the 4*D B of row data each id drags through HBM; launch count and look-back
 // latency are what matter, hence the 1+passes launch structure.
+#include <algorithm>
+#include <cstdlib>
+
 #include "common.cuh"
 #include "internal.h"
 
@@ -80,8 +83,8 @@ k_prepare(const int64_t* __restrict__ rows, int n, uint32_t height, int passes,
       keys[i] = key;
     }
     for (int p = 0; p < passes; ++p) {
-      const uint32_t digit = valid ? ((key >> (p * kRadixBits)) & (kRadix - 1)) : kNoKey;
-      const uint32_t peers = __match_any_sync(0xffffffffu, digit);
+      const uint32_t digit = valid ? ((key >> (p * kRadixBits)) & (kRadix - 1)) : 0u;
+      const uint32_t peers = match_digit<kRadixBits>(digit, valid);
       if (valid && lane == __ffs(peers) - 1) atomicAdd(&sh[p * kRadix + digit], __popc(peers));
     }
   }
@@ -122,9 +125,9 @@ k_radix_pass(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ 
 #pragma unroll
   for (int j = 0; j < kSortItems; ++j) {
     const bool valid = (warp_start + j * 32 + lane) < n;
-    const uint32_t digit = valid ? ((key[j] >> shift) & (kRadix - 1)) : kNoKey;
-    const uint32_t peers = __match_any_sync(0xffffffffu, digit);
-    const int leader = __ffs(peers) - 1;
+    const uint32_t digit = valid ? ((key[j] >> shift) & (kRadix - 1)) : 0u;
+    const uint32_t peers = match_digit<kRadixBits>(digit, valid);
+    const int leader = valid ? __ffs(peers) - 1 : lane;
     uint32_t old = 0;
     if (valid && lane == leader) {
       old = s_cnt[warp][digit];
@@ -299,9 +302,21 @@ SortedPlan plan_view(int64_t height, char* ws, const Workspace& L) {
 
 cudaError_t launch_plan(const int64_t* rows, int64_t n, int64_t height, char* ws,
                         const Workspace& L, int32_t* status, cudaStream_t s, SortedPlan* out) {
+  const int passes = sort_passes(height);
+  // small batches: the whole sort in one cluster launch (cluster_sort.cu)
+  static const bool force_global = std::getenv("B200EMB_FORCE_GLOBAL_SORT") != nullptr;
+  if (!force_global && cluster_sort_fits(n)) {
+    cudaError_t ce = launch_cluster_sort(
+        rows, n, height, passes, reinterpret_cast<uint32_t*>(ws + L.off_keys[passes & 1]),
+        reinterpret_cast<uint32_t*>(ws + L.off_perm[passes & 1]), status, s);
+    if (ce == cudaSuccess) {
+      if (out) *out = plan_view(height, ws, L);
+      return cudaSuccess;
+    }
+    if (ce != cudaErrorNotSupported) return ce;
+  }
   cudaError_t e = cudaMemsetAsync(ws, 0, L.zero_bytes, s);
   if (e != cudaSuccess) return e;
-  const int passes = sort_passes(height);
   uint32_t* keys[2] = {reinterpret_cast<uint32_t*>(ws + L.off_keys[0]),
                        reinterpret_cast<uint32_t*>(ws + L.off_keys[1])};
   uint32_t* perm[2] = {reinterpret_cast<uint32_t*>(ws + L.off_perm[0]),
@@ -310,7 +325,7 @@ cudaError_t launch_plan(const int64_t* rows, int64_t n, int64_t height, char* ws
   uint32_t* tickets = reinterpret_cast<uint32_t*>(ws + L.off_tickets);
   uint32_t* lookback = reinterpret_cast<uint32_t*>(ws + L.off_lookback);
   const int ni = static_cast<int>(n);
-  const int prep_grid = static_cast<int>(std::min<int64_t>(ceil_div(n, 256), 148 * 8));
+  const int prep_grid = static_cast<int>(std::min<int64_t>(ceil_div(n, 256 * 4), 148 * 4));
   k_prepare<<<prep_grid, 256, 0, s>>>(rows, ni, static_cast<uint32_t>(height), passes, keys[0],
                                       ghist, status);
   const int tiles = static_cast<int>(L.sort_tiles);

@@ -75,6 +75,8 @@ SHAPES = [  # (n, v, d, dist)
     (20000, 100000, 128, "zipf"), (6000, 900, 256, "zipf"), (3000, 17, 300, "uniform"),
     (4097, 1 << 20, 64, "same"), (9000, 9000, 64, "unique"), (2500, 70000, 520, "zipf"),
     (70000, 1 << 17, 8, "zipf"), (1500, 3000, 1028, "uniform"),
+    # beyond the single-cluster sort's capacity (139 264 ids): multi-launch radix sort path
+    (250000, 1 << 20, 16, "zipf"), (700000, 5000000, 8, "zipf"),
 ]
 
 
@@ -265,7 +267,11 @@ def test_sparse_sgd(capi, case, dtype):
     ur, l1u = oracle.merge_add(rows, np.abs(grad), truth=True)
     l1[ur] = l1u
     rt = FAST_RTOL if dtype == np.float32 else 1e-14
-    err = np.abs(host(p).astype(np.float64) - want.astype(np.float64))
+    # held to the fp64 evaluation of the same update: on long duplicate runs the reference's own
+    # sequential fp32 chain drifts further from it than 1e-6 relative
+    truth = base.astype(np.float64)
+    truth[ur] -= float(lr[0]) * oracle.merge_add(rows, grad, truth=True)[1]
+    err = np.abs(host(p).astype(np.float64) - truth)
     assert (err <= rt * (np.abs(base) + float(lr[0]) * l1) + 1e-30).all()
     untouched = np.setdiff1d(np.arange(v), rows)
     assert_bit_equal(host(p)[untouched], base[untouched], "sgd untouched rows")
