@@ -207,19 +207,24 @@ def run_single(args):
     side = torch.cuda.Stream(dev)
 
     def step(b):
-        """fwd gather || sort plan (side stream), then the fused reduce+update."""
+        """One step on batch b.  The sort plan of the NEXT batch (ids only, like a data-loader prefetch)
+        runs on the side stream while this batch's gather + fused reduce/update run on the main one;
+        every step still launches exactly one plan, one gather, one update."""
+        nb = (b + 1) % N_ROTATE
         side.wait_stream(main)
         with torch.cuda.stream(side):
-            capi.plan_rows(ids[b], v, ws[b], status)
+            capi.plan_rows(ids[nb], v, ws[nb], status)
         capi.lookup_table(table, ids[b], -1, out[b], status)
-        main.wait_stream(side)
         # lookup_table_grad (sparse): the SelectedRows gradient aliases ids / dOut — zero copy
         capi.sparse_sgd(table, ids[b], dout[b], lr, ws[b], capi.PLAN_READY, status)
+        main.wait_stream(side)
 
     kernels_per_step = 1 + capi.plan_kernel_count(n, v) + 2  # gather, sort plan, chunk reduce, fixup
 
     graphs = []
     with torch.cuda.stream(main):
+        for b in range(N_ROTATE):   # every workspace holds its batch's plan before the first step
+            capi.plan_rows(ids[b], v, ws[b], status)
         for b in range(N_ROTATE):   # warm every path once outside capture
             step(b)
         main.synchronize()
@@ -311,7 +316,7 @@ def run_single(args):
                    "unique_ids_per_step": u_mean, "optimizer": opt, "mode": "fast (fixed-tree reduction)",
                    "l2": "inputs rotate over %d batch buffers (%.0f MB ids+dOut+Out) > 126 MB L2; table 256 MB"
                          % (N_ROTATE, N_ROTATE * (n * 8 + 2 * n * d * 4) / 1e6),
-                   "launch": "one CUDA graph per batch buffer; sort plan on a side stream overlapping the gather"},
+                   "launch": "one CUDA graph per batch buffer; the sort plan of batch i+1 runs on a side stream during step i (ids-only prefetch), gather+update of batch i on the main stream"},
         "roofline": roofline, "phases": phases, "cpu_baseline": {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")},
         "e2e": e2e, "gpu_launches": kernels_per_step * args.steps, "clocks": clocks, "status_word": st,
     }

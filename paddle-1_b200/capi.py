@@ -80,19 +80,20 @@ def _need_cuda(*tensors):
             raise B200EmbError("b200emb ops need contiguous tensors")
 
 
-def radix_passes(height):
-    """Number of 8-bit radix passes the sort plan runs for ids in [0, height] (sort.cu key_bits)."""
+def radix_passes(n, height):
+    """Radix passes of the sort plan (sort.cu digit_plan): <=10-bit digits up to 64 tiles of 2048, else 8-bit."""
     bits = 1
     while (1 << bits) <= int(height):
         bits += 1
-    return (bits + 7) // 8
+    maxb = 10 if (n + 2047) // 2048 <= 64 else 8
+    return (bits + maxb - 1) // maxb
 
 
 def plan_kernel_count(n, height):
-    """Kernels one sort plan launches: 1 (cluster sort, n <= 16*8704) else prepare + radix passes."""
-    if 0 < n <= 16 * 8704 and "B200EMB_FORCE_GLOBAL_SORT" not in os.environ:
+    """Kernels one sort plan launches: prepare + radix passes (1 with B200EMB_CLUSTER_SORT set)."""
+    if 0 < n <= 16 * 8704 and "B200EMB_CLUSTER_SORT" in os.environ:
         return 1
-    return 1 + radix_passes(height)
+    return 1 + radix_passes(n, height)
 
 
 def workspace_bytes(n, d, elem_size=4):

@@ -54,7 +54,7 @@ int run_update(const int64_t* rows, const T* value, int64_t n, int64_t d, int64_
   SortedPlan plan;
   cudaError_t e;
   if (flags & B200EMB_PLAN_READY) {
-    plan = plan_view(height, ws, L);
+    plan = plan_view(n, height, ws, L);
   } else {
     e = launch_plan(rows, n, height, ws, L, status, s, &plan);
     if (e != cudaSuccess) return fail_cuda(e);

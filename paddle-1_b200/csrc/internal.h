@@ -26,9 +26,9 @@ inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 // Everything the kernels keep in the caller's workspace.  Offsets in bytes.
 struct Workspace {
   // zeroed at the start of every plan
-  size_t off_hist;        // u32 [kMaxPasses][kRadix]   global digit histograms
+  size_t off_hist;        // u32 [passes][bins]         global digit histograms (<= 3 x 4096)
   size_t off_tickets;     // u32 [8]                    dynamic tile counters (4 sort passes, 1 scan)
-  size_t off_lookback;    // u32 [kMaxPasses][sort_tiles][kRadix]
+  size_t off_lookback;    // u32 [passes][sort_tiles][bins]
   size_t off_scan_state;  // u32 [scan_tiles]
   size_t zero_bytes;      // bytes [0, zero_bytes) are cleared by cudaMemsetAsync
   // plan
@@ -62,7 +62,7 @@ struct SortedPlan {      // device pointers into the workspace after plan_rows
 // sort.cu
 cudaError_t launch_plan(const int64_t* rows, int64_t n, int64_t height, char* ws,
                         const Workspace& L, int32_t* status, cudaStream_t s, SortedPlan* out);
-SortedPlan plan_view(int64_t height, char* ws, const Workspace& L);
+SortedPlan plan_view(int64_t n, int64_t height, char* ws, const Workspace& L);
 cudaError_t launch_head_scan(const SortedPlan& plan, int64_t n, uint32_t invalid_key, char* ws,
                              const Workspace& L, int64_t* out_rows, int64_t* n_unique_out,
                              cudaStream_t s);

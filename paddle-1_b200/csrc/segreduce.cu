@@ -23,6 +23,7 @@
 // reference CPU loops bit for bit.  Its critical path is the longest duplicate run; it is the
 // parity mode, not the speed mode.
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "internal.h"
@@ -57,13 +58,42 @@ __device__ __forceinline__ void zero_acc(T (&a)[NV][EPV]) {
     for (int e = 0; e < EPV; ++e) a[k][e] = T(0);
 }
 
-// Consume one fully reduced row.  `eref` = any sorted position inside the segment.
+// The consumer of one fully reduced row is split in two so that callers can issue the state
+// loads (parameter / moment rows) of several rows together with the gradient-row loads and pay
+// one memory round trip per batch instead of one per row.
+template <UpdateOp OP> struct NumState {
+  static constexpr int value = OP == UpdateOp::kAdam ? 3 : (OP == UpdateOp::kMergeAdd ? 0 : 1);
+};
+template <typename T, UpdateOp OP, int NV, int EPV>
+struct RowState { T v[NumState<OP>::value == 0 ? 1 : NumState<OP>::value][NV][EPV]; };
+
 template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
-__device__ __forceinline__ void consume(const Params<T>& P, uint32_t key, uint32_t eref, int col0,
-                                        int l, const T (&acc)[NV][Epv<T, VEC>::value]) {
+__device__ __forceinline__ void load_state(const Params<T>& P, uint32_t key, int col0, int l,
+                                           RowState<T, OP, NV, Epv<T, VEC>::value>& st) {
+  constexpr int EPV = Epv<T, VEC>::value;
+  if constexpr (OP == UpdateOp::kMergeAdd) return;
+  if (key >= P.height) return;
+  const int64_t base = static_cast<int64_t>(key) * P.d;
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    const int col = col0 + (l + k * LPR) * EPV;
+    if (col >= P.d) continue;
+    load_vec<T, VEC>(P.param + base + col, st.v[0][k]);
+    if constexpr (OP == UpdateOp::kAdam) {
+      load_vec<T, VEC>(P.m1 + base + col, st.v[1][k]);
+      load_vec<T, VEC>(P.m2 + base + col, st.v[2][k]);
+    }
+  }
+}
+
+// `eref` = any sorted position inside the segment (kMergeAdd looks its output row up there).
+template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
+__device__ __forceinline__ void apply_state(const Params<T>& P, uint32_t key, uint32_t eref, int col0,
+                                            int l, const T (&acc)[NV][Epv<T, VEC>::value],
+                                            RowState<T, OP, NV, Epv<T, VEC>::value>& st) {
   constexpr int EPV = Epv<T, VEC>::value;
   using A = Arith<T>;
-  if (key >= P.height) return;  // out-of-range row: flagged by k_prepare, skipped here
+  if (key >= P.height) return;  // out-of-range row: flagged by the sort plan, skipped here
   const int64_t row = (OP == UpdateOp::kMergeAdd) ? static_cast<int64_t>(P.uidx[eref])
                                                   : static_cast<int64_t>(key);
   const int64_t base = row * P.d;
@@ -74,49 +104,52 @@ __device__ __forceinline__ void consume(const Params<T>& P, uint32_t key, uint32
     if constexpr (OP == UpdateOp::kMergeAdd) {
       store_vec<T, VEC>(P.param + base + col, acc[k]);
     } else if constexpr (OP == UpdateOp::kAddToTensor) {
-      T t[EPV];
-      load_vec<T, VEC>(P.param + base + col, t);
 #pragma unroll
-      for (int e = 0; e < EPV; ++e) t[e] = A::add(t[e], acc[k][e]);
-      store_vec<T, VEC>(P.param + base + col, t);
+      for (int e = 0; e < EPV; ++e) st.v[0][k][e] = A::add(st.v[0][k][e], acc[k][e]);
+      store_vec<T, VEC>(P.param + base + col, st.v[0][k]);
     } else if constexpr (OP == UpdateOp::kSgd) {
-      T p[EPV];
-      load_vec<T, VEC>(P.param + base + col, p);
       const T lr = *P.lr;
 #pragma unroll
-      for (int e = 0; e < EPV; ++e) p[e] = A::sub(p[e], A::mul(lr, acc[k][e]));
-      store_vec<T, VEC>(P.param + base + col, p);
+      for (int e = 0; e < EPV; ++e) st.v[0][k][e] = A::sub(st.v[0][k][e], A::mul(lr, acc[k][e]));
+      store_vec<T, VEC>(P.param + base + col, st.v[0][k]);
     } else {  // kAdam — operation order of adam_op.h:209-213, every step rounded in T
-      T p[EPV], m1[EPV], m2[EPV];
-      load_vec<T, VEC>(P.param + base + col, p);
-      load_vec<T, VEC>(P.m1 + base + col, m1);
-      load_vec<T, VEC>(P.m2 + base + col, m2);
       const T one = T(1);
       const T lr_t = A::mul(*P.lr, A::div(A::sqrt(A::sub(one, *P.b2p)), A::sub(one, *P.b1p)));
       const T omb1 = A::sub(one, P.beta1), omb2 = A::sub(one, P.beta2);
 #pragma unroll
       for (int e = 0; e < EPV; ++e) {
         const T g = acc[k][e];
-        m1[e] = A::add(A::mul(P.beta1, m1[e]), A::mul(omb1, g));
-        m2[e] = A::add(A::mul(P.beta2, m2[e]), A::mul(A::mul(omb2, g), g));
-        p[e] = A::sub(p[e], A::mul(lr_t, A::div(m1[e], A::add(A::sqrt(m2[e]), P.eps))));
+        const T m1 = A::add(A::mul(P.beta1, st.v[1][k][e]), A::mul(omb1, g));
+        const T m2 = A::add(A::mul(P.beta2, st.v[2][k][e]), A::mul(A::mul(omb2, g), g));
+        st.v[0][k][e] = A::sub(st.v[0][k][e], A::mul(lr_t, A::div(m1, A::add(A::sqrt(m2), P.eps))));
+        st.v[1][k][e] = m1;
+        st.v[2][k][e] = m2;
       }
-      store_vec<T, VEC>(P.m1 + base + col, m1);
-      store_vec<T, VEC>(P.m2 + base + col, m2);
-      store_vec<T, VEC>(P.param + base + col, p);
+      store_vec<T, VEC>(P.m1 + base + col, st.v[1][k]);
+      store_vec<T, VEC>(P.m2 + base + col, st.v[2][k]);
+      store_vec<T, VEC>(P.param + base + col, st.v[0][k]);
     }
   }
 }
 
+template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
+__device__ __forceinline__ void consume(const Params<T>& P, uint32_t key, uint32_t eref, int col0,
+                                        int l, const T (&acc)[NV][Epv<T, VEC>::value]) {
+  RowState<T, OP, NV, Epv<T, VEC>::value> st;
+  load_state<T, OP, LPR, NV, VEC>(P, key, col0, l, st);
+  apply_state<T, OP, LPR, NV, VEC>(P, key, eref, col0, l, acc, st);
+}
+
 // ------------------------------------------------------------------------------------------
 template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
-__global__ void __launch_bounds__(kBlock, 4)
+__global__ void __launch_bounds__(kBlock, 2)
 k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ perm, int n,
                int chunk, const T* __restrict__ value, Params<T> P, Carry<T> C) {
   constexpr int EPV = Epv<T, VEC>::value;
   constexpr int GPC = kBlock / LPR;
   constexpr int COLS = LPR * NV * EPV;
-  constexpr int kBatch = NV == 1 ? 8 : 4;  // independent gradient rows in flight per group
+  // gradient rows (+ the state rows of segments closing among them) in flight per group
+  constexpr int kBatch = NV == 1 ? (NumState<OP>::value <= 1 ? 8 : 4) : (NV == 2 ? 4 : 2);
   using A = Arith<T>;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T* s_head = reinterpret_cast<T*>(smem_raw);                 // [GPC][COLS]
@@ -150,67 +183,83 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
     if (active) {
       const uint32_t prev = gs > 0 ? s_key[gs - 1] : s_prev_key;
       const uint32_t next = ge < cta_count ? s_key[ge] : s_next_key;
-      uint32_t cur = s_key[gs];
-      bool first = true;
+      bool first = true;   // no segment has closed inside this chunk yet
       T acc[NV][EPV];
       zero_acc<T, NV, EPV>(acc);
-
-      auto flush = [&](bool right_open, int e_last) {
-        const bool left_open = first && cur == prev;
-        if (!left_open && !right_open) {
-          consume<T, OP, LPR, NV, VEC>(P, cur, static_cast<uint32_t>(cta_start + e_last), col0, l, acc);
-        } else {
-          T* dst = (left_open ? s_head : s_tail) + g * COLS;
-#pragma unroll
-          for (int k = 0; k < NV; ++k)
-#pragma unroll
-            for (int e = 0; e < EPV; ++e) dst[(l + k * LPR) * EPV + e] = acc[k][e];
-          if (left_open) {
-            flags |= kHead | (right_open ? kThrough : 0u);
-          } else {
-            flags |= kTail;
-            tail_key = cur;
-            tail_eref = static_cast<uint32_t>(cta_start + e_last);
-          }
-        }
-      };
-
       for (int e0 = gs; e0 < ge; e0 += kBatch) {
+        // Everything about segment structure comes from the keys already in shared memory, so the
+        // batch's gradient rows AND the state rows of every segment that closes inside it are
+        // requested together: one round trip per batch.
         uint32_t k[kBatch];
-        T r[kBatch][NV][EPV];
+        bool in[kBatch], closes[kBatch], direct[kBatch];
+        bool f = first;
 #pragma unroll
         for (int b = 0; b < kBatch; ++b) {
           const int idx = e0 + b;
-          const bool in = idx < ge;
-          k[b] = in ? s_key[idx] : cur;
-          const int64_t src = in ? static_cast<int64_t>(s_perm[idx]) * d : 0;
+          in[b] = idx < ge;
+          k[b] = in[b] ? s_key[idx] : kNoKey;
+          const uint32_t kn = (idx + 1 < ge) ? s_key[idx + 1] : next;
+          closes[b] = in[b] && k[b] != kn;
+          direct[b] = closes[b] && !(f && k[b] == prev);
+          f = f && !closes[b];
+        }
+        T r[kBatch][NV][EPV];
+        RowState<T, OP, NV, EPV> st[kBatch];
+#pragma unroll
+        for (int b = 0; b < kBatch; ++b) {
+          const int idx = e0 + b;
+          const int64_t src = in[b] ? static_cast<int64_t>(s_perm[idx]) * d : 0;
 #pragma unroll
           for (int kk = 0; kk < NV; ++kk) {
             const int col = col0 + (l + kk * LPR) * EPV;
-            if (in && col < d) load_vec_stream<T, VEC>(value + src + col, r[b][kk]);
+            if (in[b] && col < d) load_vec_stream<T, VEC>(value + src + col, r[b][kk]);
             else {
 #pragma unroll
               for (int e = 0; e < EPV; ++e) r[b][kk][e] = T(0);
             }
           }
+          if (direct[b]) load_state<T, OP, LPR, NV, VEC>(P, k[b], col0, l, st[b]);
         }
 #pragma unroll
         for (int b = 0; b < kBatch; ++b) {
-          if (e0 + b < ge) {
-            if (k[b] != cur) {
-              flush(false, e0 + b - 1);
-              zero_acc<T, NV, EPV>(acc);
-              cur = k[b];
-              first = false;
-            }
+          if (in[b]) {
 #pragma unroll
             for (int kk = 0; kk < NV; ++kk)
 #pragma unroll
               for (int e = 0; e < EPV; ++e) acc[kk][e] = A::add(acc[kk][e], r[b][kk][e]);
+            if (closes[b]) {
+              if (direct[b]) {
+                apply_state<T, OP, LPR, NV, VEC>(P, k[b], static_cast<uint32_t>(cta_start + e0 + b),
+                                                 col0, l, acc, st[b]);
+              } else {  // first segment of the chunk, entered from the previous chunk
+#pragma unroll
+                for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+                  for (int e = 0; e < EPV; ++e) s_head[g * COLS + (l + kk * LPR) * EPV + e] = acc[kk][e];
+                flags |= kHead;
+              }
+              zero_acc<T, NV, EPV>(acc);
+              first = false;
+            }
           }
         }
       }
-      flush(cur == next, ge - 1);
+      const uint32_t last = s_key[ge - 1];
+      if (last == next) {  // the chunk ends inside a segment: leave a partial sum
+        const bool left_open = first && last == prev;
+        T* dst = (left_open ? s_head : s_tail) + g * COLS;
+#pragma unroll
+        for (int kk = 0; kk < NV; ++kk)
+#pragma unroll
+          for (int e = 0; e < EPV; ++e) dst[(l + kk * LPR) * EPV + e] = acc[kk][e];
+        if (left_open) {
+          flags |= kHead | kThrough;
+        } else {
+          flags |= kTail;
+          tail_key = last;
+          tail_eref = static_cast<uint32_t>(cta_start + ge - 1);
+        }
+      }
     }
     if (l == 0) s_flags[g] = flags;
     __syncthreads();
@@ -509,7 +558,11 @@ cudaError_t launch_op(const SortedPlan& plan, const T* value, int64_t n, int64_t
           occ = 4;
         occ_cache = occ;
       }
-      const int chunk = choose_chunk(n, GPC * occ_cache);
+      int chunk = choose_chunk(n, GPC * occ_cache);
+      if (const char* ov = std::getenv("B200EMB_CHUNK")) {  // tuning override
+        const int c = std::atoi(ov);
+        if (c >= kMinChunk && c <= kMaxChunk) chunk = c;
+      }
       const int ctas = static_cast<int>(ceil_div(n, static_cast<int64_t>(GPC) * chunk));
       const size_t smem = sizeof(T) * 2 * GPC * COLS + sizeof(uint32_t) * 2 * GPC * chunk;
       k_chunk_reduce<T, OP, LPR, NV, VEC><<<ctas, kBlock, smem, s>>>(plan.keys, plan.perm, ni, chunk,

@@ -23,14 +23,20 @@
 namespace b200emb {
 
 namespace {
+#ifdef B200EMB_PROFILE
+__device__ long long g_sort_prof[256][8];
+#define SORT_STAMP(i) do { if (threadIdx.x == 0 && tile < 256) g_sort_prof[tile][i] = clock64(); } while (0)
+#else
+#define SORT_STAMP(i) do { } while (0)
+#endif
 constexpr uint32_t kFlagAgg = 1u << 30;
 constexpr uint32_t kFlagIncl = 2u << 30;
 constexpr uint32_t kValMask = (1u << 30) - 1;
-constexpr int kLookBatch = 16;
 
 // Walk back over predecessor tiles' published words (one counter per tile, `stride` words
 // apart) until an inclusive prefix is met.  Loads are issued kLookBatch at a time so the walk
 // costs one L2 round trip per batch rather than per tile.
+template <int kLookBatch = 16>
 __device__ __forceinline__ uint32_t look_back(const uint32_t* state, int tile, size_t stride) {
   uint32_t excl = 0;
   int t = tile - 1;
@@ -62,19 +68,105 @@ __device__ __forceinline__ uint32_t look_back(const uint32_t* state, int tile, s
   return excl;
 }
 
+// K consecutive counters per tile (one thread's bins), fetched with 16-byte loads, LB tiles in
+// flight per round trip.  Each 32-bit word carries its own flag, so torn vectors are harmless.
+template <int K>
+__device__ __forceinline__ void ld_state_vec(const uint32_t* p, uint32_t (&v)[K]) {
+  if constexpr (K == 1) {
+    v[0] = ld_relaxed(p);
+  } else if constexpr (K == 2) {
+    asm volatile("ld.volatile.global.v2.u32 {%0,%1}, [%2];" : "=r"(v[0]), "=r"(v[1]) : "l"(p) : "memory");
+  } else {
+#pragma unroll
+    for (int q = 0; q < K / 4; ++q)
+      asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+                   : "=r"(v[4 * q]), "=r"(v[4 * q + 1]), "=r"(v[4 * q + 2]), "=r"(v[4 * q + 3])
+                   : "l"(p + 4 * q) : "memory");
+  }
+}
+
+// plain (non-polling) vector load of K counters, L2-cached only
+template <int K>
+__device__ __forceinline__ void ld_cg_vec(const uint32_t* p, uint32_t (&v)[K]) {
+  if constexpr (K == 1) {
+    v[0] = __ldcg(p);
+  } else if constexpr (K == 2) {
+    const uint2 t = __ldcg(reinterpret_cast<const uint2*>(p));
+    v[0] = t.x; v[1] = t.y;
+  } else {
+#pragma unroll
+    for (int q = 0; q < K / 4; ++q) {
+      const uint4 t = __ldcg(reinterpret_cast<const uint4*>(p) + q);
+      v[4 * q] = t.x; v[4 * q + 1] = t.y; v[4 * q + 2] = t.z; v[4 * q + 3] = t.w;
+    }
+  }
+}
+
+template <int K, int LB>
+__device__ __forceinline__ void look_back_vec(const uint32_t* state, int tile, size_t stride,
+                                              uint32_t (&excl)[K]) {
+  bool fin[K];
+#pragma unroll
+  for (int k = 0; k < K; ++k) fin[k] = false;
+  int t = tile - 1;
+  while (t >= 0) {
+    uint32_t v[LB][K];
+#pragma unroll
+    for (int i = 0; i < LB; ++i) {
+      const int tt = t - i;
+      if (tt >= 0) {
+        ld_state_vec<K>(state + static_cast<size_t>(tt) * stride, v[i]);
+      } else {
+#pragma unroll
+        for (int k = 0; k < K; ++k) v[i][k] = kFlagIncl;
+      }
+    }
+    int adv = 0;
+    bool stall = false, all_fin = false;
+#pragma unroll
+    for (int i = 0; i < LB; ++i) {
+      if (!stall && !all_fin) {
+        bool ready = true;
+#pragma unroll
+        for (int k = 0; k < K; ++k) ready = ready && (fin[k] || (v[i][k] >> 30) != 0);
+        if (!ready) {
+          stall = true;
+        } else {
+          all_fin = true;
+#pragma unroll
+          for (int k = 0; k < K; ++k) {
+            if (!fin[k]) {
+              excl[k] += v[i][k] & kValMask;
+              fin[k] = (v[i][k] >> 30) == 2;
+            }
+            all_fin = all_fin && fin[k];
+          }
+          ++adv;
+        }
+      }
+    }
+    if (all_fin) break;
+    t -= adv;
+  }
+}
+
+// Digit width is a template parameter: 8 bits for large N (small look-back state), up to 12 bits
+// for small N where every pass saved is a launch + chained scan saved.
+template <int BITS>
 __global__ void __launch_bounds__(256)
 k_prepare(const int64_t* __restrict__ rows, int n, uint32_t height, int passes,
           uint32_t* __restrict__ keys, uint32_t* __restrict__ ghist, int32_t* status) {
-  __shared__ uint32_t sh[kMaxPasses * kRadix];
+  constexpr int kBins = 1 << BITS;
+  extern __shared__ uint32_t sh[];   // [passes][kBins]
   const int tid = threadIdx.x, lane = tid & 31;
-  for (int i = tid; i < passes * kRadix; i += blockDim.x) sh[i] = 0;
+  for (int i = tid; i < passes * kBins; i += blockDim.x) sh[i] = 0;
   __syncthreads();
   bool bad = false;
   const int stride = gridDim.x * blockDim.x;
   for (int base = blockIdx.x * blockDim.x; base < n; base += stride) {
     const int i = base + tid;
     const bool valid = i < n;
-    uint32_t key = kNoKey;
+    uint32_t key = 0;
     if (valid) {
       const int64_t r = rows[i];
       const bool ok = r >= 0 && r < static_cast<int64_t>(height);
@@ -83,81 +175,106 @@ k_prepare(const int64_t* __restrict__ rows, int n, uint32_t height, int passes,
       keys[i] = key;
     }
     for (int p = 0; p < passes; ++p) {
-      const uint32_t digit = valid ? ((key >> (p * kRadixBits)) & (kRadix - 1)) : 0u;
-      const uint32_t peers = match_digit<kRadixBits>(digit, valid);
-      if (valid && lane == __ffs(peers) - 1) atomicAdd(&sh[p * kRadix + digit], __popc(peers));
+      const uint32_t digit = (key >> (p * BITS)) & (kBins - 1);
+      const uint32_t peers = match_digit<BITS>(digit, valid);
+      if (valid && lane == __ffs(peers) - 1) atomicAdd(&sh[p * kBins + digit], __popc(peers));
     }
   }
   __syncthreads();
-  for (int i = tid; i < passes * kRadix; i += blockDim.x)
+  for (int i = tid; i < passes * kBins; i += blockDim.x)
     if (sh[i]) atomicAdd(&ghist[i], sh[i]);
   if (bad && status) atomicOr(status, 2);
 }
 
-template <bool HAS_PERM_IN>
+template <int BITS, bool HAS_PERM_IN>
 __global__ void __launch_bounds__(kSortThreads)
 k_radix_pass(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ perm_in,
              uint32_t* __restrict__ keys_out, uint32_t* __restrict__ perm_out, int n, int shift,
              const uint32_t* __restrict__ ghist, uint32_t* ticket, uint32_t* state) {
   constexpr int kWarps = kSortThreads / 32;
-  __shared__ uint32_t s_cnt[kWarps][kRadix];
-  __shared__ uint32_t s_base[kRadix];
+  constexpr int kBins = 1 << BITS;
+  constexpr int K = kBins / kSortThreads;          // bins owned by one thread (consecutive)
+  constexpr int kLb = K >= 8 ? 4 : (K == 4 ? 12 : 16);  // predecessor tiles in flight
+  extern __shared__ __align__(16) unsigned char sort_smem[];
+  uint32_t* s_base = reinterpret_cast<uint32_t*>(sort_smem);            // [kBins]
+  uint16_t* s_cnt = reinterpret_cast<uint16_t*>(s_base + kBins);        // [kWarps][kBins]
   __shared__ uint32_t s_warp_sum[kWarps];
   __shared__ int s_tile;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) s_tile = static_cast<int>(atomicAdd(ticket, 1u));
-#pragma unroll
-  for (int w = 0; w < kWarps; ++w) s_cnt[w][tid] = 0;
+  {
+    uint32_t* z = reinterpret_cast<uint32_t*>(s_cnt);
+    for (int i = tid; i < kWarps * kBins / 2; i += kSortThreads) z[i] = 0;
+  }
   __syncthreads();
   const int tile = s_tile;
   const int warp_start = tile * kSortTile + warp * (32 * kSortItems);
+  uint16_t* my_cnt = s_cnt + warp * kBins;
+  SORT_STAMP(0);
 
   uint32_t key[kSortItems], pm[kSortItems], rank[kSortItems];
 #pragma unroll
   for (int j = 0; j < kSortItems; ++j) {
     const int idx = warp_start + j * 32 + lane;
     const bool valid = idx < n;
-    key[j] = valid ? keys_in[idx] : kNoKey;
+    key[j] = valid ? keys_in[idx] : 0u;
     pm[j] = valid ? (HAS_PERM_IN ? perm_in[idx] : static_cast<uint32_t>(idx)) : 0u;
   }
   // stable rank inside the warp: items are ordered (j, lane) == ascending idx
   const uint32_t lt = lanemask_lt();
+  SORT_STAMP(1);
 #pragma unroll
   for (int j = 0; j < kSortItems; ++j) {
     const bool valid = (warp_start + j * 32 + lane) < n;
-    const uint32_t digit = valid ? ((key[j] >> shift) & (kRadix - 1)) : 0u;
-    const uint32_t peers = match_digit<kRadixBits>(digit, valid);
+    const uint32_t digit = (key[j] >> shift) & (kBins - 1);
+    const uint32_t peers = match_digit<BITS>(digit, valid);
     const int leader = valid ? __ffs(peers) - 1 : lane;
     uint32_t old = 0;
     if (valid && lane == leader) {
-      old = s_cnt[warp][digit];
-      s_cnt[warp][digit] = old + __popc(peers);
+      old = my_cnt[digit];
+      my_cnt[digit] = static_cast<uint16_t>(old + __popc(peers));
     }
     old = __shfl_sync(0xffffffffu, old, leader);
     rank[j] = old + __popc(peers & lt);
     __syncwarp();
   }
   __syncthreads();
-  // bin `tid`: exclusive offsets of each warp inside the tile, tile total
-  uint32_t total = 0;
+  SORT_STAMP(2);
+  // bins tid*K .. tid*K+K-1: exclusive offsets of each warp inside the tile, tile totals
+  uint32_t total[K], excl[K];
 #pragma unroll
-  for (int w = 0; w < kWarps; ++w) {
-    const uint32_t c = s_cnt[w][tid];
-    s_cnt[w][tid] = total;
-    total += c;
+  for (int k = 0; k < K; ++k) {
+    const int bin = tid * K + k;
+    uint32_t t = 0;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) {
+      const uint32_t c = s_cnt[w * kBins + bin];
+      s_cnt[w * kBins + bin] = static_cast<uint16_t>(t);
+      t += c;
+    }
+    total[k] = t;
+    excl[k] = 0;
   }
-  uint32_t* my_state = state + static_cast<size_t>(tile) * kRadix + tid;
-  uint32_t excl = 0;
+  uint32_t* my_state = state + static_cast<size_t>(tile) * kBins + tid * K;
+  uint32_t g[K], gsum = 0;   // global histogram of this thread's bins (fetched ahead of the look-back)
+#pragma unroll
+  for (int k = 0; k < K; ++k) g[k] = ghist[tid * K + k];
+  SORT_STAMP(3);
   if (tile == 0) {
-    st_relaxed(my_state, kFlagIncl | total);
+#pragma unroll
+    for (int k = 0; k < K; ++k) st_relaxed(my_state + k, kFlagIncl | total[k]);
   } else {
-    st_relaxed(my_state, kFlagAgg | total);
-    excl = look_back(state + tid, tile, kRadix);
-    st_relaxed(my_state, kFlagIncl | (excl + total));
+#pragma unroll
+    for (int k = 0; k < K; ++k) st_relaxed(my_state + k, kFlagAgg | total[k]);
+    look_back_vec<K, kLb>(state + tid * K, tile, kBins, excl);
+#pragma unroll
+    for (int k = 0; k < K; ++k) st_relaxed(my_state + k, kFlagIncl | (excl[k] + total[k]));
   }
-  // exclusive scan of the global histogram over bins
-  uint32_t g = ghist[tid];
-  uint32_t incl = g;
+  SORT_STAMP(4);
+  // exclusive scan of the global histogram over bins (thread-local K, then warp, then block)
+#pragma unroll
+  for (int k = 0; k < K; ++k) gsum += g[k];
+  uint32_t incl = gsum;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
     const uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
@@ -165,19 +282,191 @@ k_radix_pass(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ 
   }
   if (lane == 31) s_warp_sum[warp] = incl;
   __syncthreads();
-  uint32_t warp_off = 0;
+  uint32_t run = incl - gsum;
 #pragma unroll
-  for (int w = 0; w < kWarps; ++w) warp_off += (w < warp) ? s_warp_sum[w] : 0u;
-  s_base[tid] = warp_off + incl - g + excl;
+  for (int w = 0; w < kWarps; ++w) run += (w < warp) ? s_warp_sum[w] : 0u;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    s_base[tid * K + k] = run + excl[k];
+    run += g[k];
+  }
+  __syncthreads();
+  SORT_STAMP(5);
+#pragma unroll
+  for (int j = 0; j < kSortItems; ++j) {
+    const int idx = warp_start + j * 32 + lane;
+    if (idx < n) {
+      const uint32_t digit = (key[j] >> shift) & (kBins - 1);
+      const uint32_t pos = s_base[digit] + my_cnt[digit] + rank[j];
+      keys_out[pos] = key[j];
+      perm_out[pos] = pm[j];
+    }
+  }
+  SORT_STAMP(6);
+}
+
+// ---- small batches (<= kDirectMaxTiles tiles): no chained scan at all --------------------
+// With at most 64 tiles every tile's per-digit counts fit a small matrix H[pass][tile][bin] in
+// L2.  k_prepare_direct fills H[0] (one CTA per tile, plain stores) and clears the later
+// passes' matrices; each pass kernel reads the whole column block of its bins (no flags, no
+// polling: the kernel boundary is the synchronisation), which yields both the exclusive prefix
+// over earlier tiles and the global digit totals, and — while scattering — counts the NEXT pass's
+// matrix with fire-and-forget integer reductions keyed by (destination tile, next digit).
+// Launches per plan: 1 + passes, no memset, no look-back.
+constexpr int kDirectMaxTiles = 64;
+
+template <int BITS>
+__global__ void __launch_bounds__(kSortThreads)
+k_prepare_direct(const int64_t* __restrict__ rows, int n, uint32_t height, int passes,
+                 uint32_t* __restrict__ keys, uint32_t* __restrict__ hmat, int32_t* status) {
+  constexpr int kBins = 1 << BITS;
+  __shared__ uint32_t sh[kBins];
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int tile = blockIdx.x, tiles = gridDim.x;
+  for (int i = tid; i < kBins; i += kSortThreads) sh[i] = 0;
+  __syncthreads();
+  bool bad = false;
+#pragma unroll
+  for (int j = 0; j < kSortItems; ++j) {
+    const int i = tile * kSortTile + j * kSortThreads + tid;
+    const bool valid = i < n;
+    uint32_t key = 0;
+    if (valid) {
+      const int64_t r = rows[i];
+      const bool ok = r >= 0 && r < static_cast<int64_t>(height);
+      key = ok ? static_cast<uint32_t>(r) : height;
+      bad |= !ok;
+      keys[i] = key;
+    }
+    const uint32_t digit = key & (kBins - 1);
+    const uint32_t peers = match_digit<BITS>(digit, valid);
+    if (valid && lane == __ffs(peers) - 1) atomicAdd(&sh[digit], __popc(peers));
+  }
+  __syncthreads();
+  for (int i = tid; i < kBins; i += kSortThreads) {
+    hmat[static_cast<size_t>(tile) * kBins + i] = sh[i];
+    for (int p = 1; p < passes; ++p)
+      hmat[(static_cast<size_t>(p) * tiles + tile) * kBins + i] = 0;
+  }
+  if (bad && status) atomicOr(status, 2);
+}
+
+template <int BITS, bool HAS_PERM_IN>
+__global__ void __launch_bounds__(kSortThreads)
+k_radix_pass_direct(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ perm_in,
+                    uint32_t* __restrict__ keys_out, uint32_t* __restrict__ perm_out, int n,
+                    int shift, const uint32_t* __restrict__ hmat, uint32_t* __restrict__ hnext) {
+  constexpr int kWarps = kSortThreads / 32;
+  constexpr int kBins = 1 << BITS;
+  constexpr int K = kBins / kSortThreads;
+  __shared__ uint32_t s_base[kBins];
+  __shared__ uint16_t s_cnt[kWarps * kBins];
+  __shared__ uint32_t s_warp_sum[kWarps];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tile = blockIdx.x, tiles = gridDim.x;
+  {
+    uint32_t* z = reinterpret_cast<uint32_t*>(s_cnt);
+    for (int i = tid; i < kWarps * kBins / 2; i += kSortThreads) z[i] = 0;
+  }
+  const int warp_start = tile * kSortTile + warp * (32 * kSortItems);
+  uint16_t* my_cnt = s_cnt + warp * kBins;
+  uint32_t key[kSortItems], pm[kSortItems], rank[kSortItems];
+#pragma unroll
+  for (int j = 0; j < kSortItems; ++j) {
+    const int idx = warp_start + j * 32 + lane;
+    const bool valid = idx < n;
+    key[j] = valid ? keys_in[idx] : 0u;
+    pm[j] = valid ? (HAS_PERM_IN ? perm_in[idx] : static_cast<uint32_t>(idx)) : 0u;
+  }
+  // column block of this thread's K bins: prefix over earlier tiles + totals over all tiles
+  uint32_t excl[K], total[K];
+#pragma unroll
+  for (int k = 0; k < K; ++k) { excl[k] = 0; total[k] = 0; }
+  constexpr int kU = K >= 4 ? 26 : 32;   // rows of the matrix in flight per round trip
+  for (int t0 = 0; t0 < tiles; t0 += kU) {
+    uint32_t v[kU][K];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int t = t0 + u;
+      if (t < tiles) {
+        ld_cg_vec<K>(hmat + static_cast<size_t>(t) * kBins + tid * K, v[u]);
+      } else {
+#pragma unroll
+        for (int k = 0; k < K; ++k) v[u][k] = 0;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u)
+#pragma unroll
+      for (int k = 0; k < K; ++k) {
+        total[k] += v[u][k];
+        excl[k] += (t0 + u < tile) ? v[u][k] : 0u;
+      }
+  }
+  __syncthreads();
+  // stable rank inside the warp: items are ordered (j, lane) == ascending idx
+  const uint32_t lt = lanemask_lt();
+#pragma unroll
+  for (int j = 0; j < kSortItems; ++j) {
+    const bool valid = (warp_start + j * 32 + lane) < n;
+    const uint32_t digit = (key[j] >> shift) & (kBins - 1);
+    const uint32_t peers = match_digit<BITS>(digit, valid);
+    const int leader = valid ? __ffs(peers) - 1 : lane;
+    uint32_t old = 0;
+    if (valid && lane == leader) {
+      old = my_cnt[digit];
+      my_cnt[digit] = static_cast<uint16_t>(old + __popc(peers));
+    }
+    old = __shfl_sync(0xffffffffu, old, leader);
+    rank[j] = old + __popc(peers & lt);
+    __syncwarp();
+  }
+  __syncthreads();
+  // exclusive offsets of each warp inside the tile
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    const int bin = tid * K + k;
+    uint32_t t = 0;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) {
+      const uint32_t c = s_cnt[w * kBins + bin];
+      s_cnt[w * kBins + bin] = static_cast<uint16_t>(t);
+      t += c;
+    }
+  }
+  // exclusive scan of the digit totals over bins
+  uint32_t gsum = 0;
+#pragma unroll
+  for (int k = 0; k < K; ++k) gsum += total[k];
+  uint32_t incl = gsum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += up;
+  }
+  if (lane == 31) s_warp_sum[warp] = incl;
+  __syncthreads();
+  uint32_t run = incl - gsum;
+#pragma unroll
+  for (int w = 0; w < kWarps; ++w) run += (w < warp) ? s_warp_sum[w] : 0u;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    s_base[tid * K + k] = run + excl[k];
+    run += total[k];
+  }
   __syncthreads();
 #pragma unroll
   for (int j = 0; j < kSortItems; ++j) {
     const int idx = warp_start + j * 32 + lane;
     if (idx < n) {
-      const uint32_t digit = (key[j] >> shift) & (kRadix - 1);
-      const uint32_t pos = s_base[digit] + s_cnt[warp][digit] + rank[j];
+      const uint32_t digit = (key[j] >> shift) & (kBins - 1);
+      const uint32_t pos = s_base[digit] + my_cnt[digit] + rank[j];
       keys_out[pos] = key[j];
       perm_out[pos] = pm[j];
+      if (hnext) {
+        const uint32_t nd = (key[j] >> (shift + BITS)) & (kBins - 1);
+        atomicAdd(hnext + static_cast<size_t>(pos / kSortTile) * kBins + nd, 1u);
+      }
     }
   }
 }
@@ -261,7 +550,26 @@ int key_bits(int64_t height) {  // keys span [0, height] (height = the invalid s
   while ((1ull << b) <= static_cast<unsigned long long>(height)) ++b;
   return b;
 }
-int sort_passes(int64_t height) { return static_cast<int>(ceil_div(key_bits(height), kRadixBits)); }
+
+// Small batches are launch/latency bound: the direct-prefix mode spends shared memory on digits
+// of up to 10 bits to save passes.  Larger batches keep 8-bit digits (the chained scan's walk
+// costs one counter per bin per predecessor tile, so wide digits lose there).
+constexpr int kDirectMaxBits = 10;
+struct DigitPlan { int passes, bits; bool direct; };
+DigitPlan digit_plan(int64_t n, int64_t height) {
+  const int kb = key_bits(height);
+  DigitPlan p;
+  p.direct = ceil_div(n, kSortTile) <= kDirectMaxTiles;
+  const int maxb = p.direct ? kDirectMaxBits : kRadixBits;
+  p.passes = static_cast<int>(ceil_div(kb, maxb));
+  p.bits = static_cast<int>(ceil_div(kb, p.passes));
+  if (p.bits < kRadixBits) p.bits = kRadixBits;
+  return p;
+}
+// counter words per tile the workspace must hold for any height at this n
+int64_t lookback_words_per_tile(int64_t n) {
+  return ceil_div(n, kSortTile) <= kDirectMaxTiles ? 4LL * (1 << kDirectMaxBits) : 4LL * kRadix;
+}
 
 }  // namespace
 
@@ -273,9 +581,9 @@ Workspace make_workspace(int64_t n, int64_t d, int64_t elem_size) {
   L.max_ctas = ceil_div(n, static_cast<int64_t>(kMinGroupsPerCta) * kMinChunk) + 1;
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes); return o; };
-  L.off_hist = take(sizeof(uint32_t) * kMaxPasses * kRadix);
+  L.off_hist = take(sizeof(uint32_t) * 4 * (1 << kDirectMaxBits));
   L.off_tickets = take(sizeof(uint32_t) * 8);
-  L.off_lookback = take(sizeof(uint32_t) * kMaxPasses * L.sort_tiles * kRadix);
+  L.off_lookback = take(sizeof(uint32_t) * L.sort_tiles * lookback_words_per_tile(n));
   L.off_scan_state = take(sizeof(uint32_t) * L.scan_tiles);
   L.zero_bytes = off;
   L.off_plan = take(sizeof(PlanHeader));
@@ -292,31 +600,19 @@ Workspace make_workspace(int64_t n, int64_t d, int64_t elem_size) {
   return L;
 }
 
-SortedPlan plan_view(int64_t height, char* ws, const Workspace& L) {
+SortedPlan plan_view(int64_t n, int64_t height, char* ws, const Workspace& L) {
   SortedPlan p;
-  p.passes = sort_passes(height);
+  p.passes = digit_plan(n, height).passes;
   p.keys = reinterpret_cast<const uint32_t*>(ws + L.off_keys[p.passes & 1]);
   p.perm = reinterpret_cast<const uint32_t*>(ws + L.off_perm[p.passes & 1]);
   return p;
 }
 
-cudaError_t launch_plan(const int64_t* rows, int64_t n, int64_t height, char* ws,
-                        const Workspace& L, int32_t* status, cudaStream_t s, SortedPlan* out) {
-  const int passes = sort_passes(height);
-  // small batches: the whole sort in one cluster launch (cluster_sort.cu)
-  static const bool force_global = std::getenv("B200EMB_FORCE_GLOBAL_SORT") != nullptr;
-  if (!force_global && cluster_sort_fits(n)) {
-    cudaError_t ce = launch_cluster_sort(
-        rows, n, height, passes, reinterpret_cast<uint32_t*>(ws + L.off_keys[passes & 1]),
-        reinterpret_cast<uint32_t*>(ws + L.off_perm[passes & 1]), status, s);
-    if (ce == cudaSuccess) {
-      if (out) *out = plan_view(height, ws, L);
-      return cudaSuccess;
-    }
-    if (ce != cudaErrorNotSupported) return ce;
-  }
-  cudaError_t e = cudaMemsetAsync(ws, 0, L.zero_bytes, s);
-  if (e != cudaSuccess) return e;
+namespace {
+template <int BITS>
+cudaError_t launch_passes(const int64_t* rows, int n, uint32_t height, int passes, char* ws,
+                          const Workspace& L, int32_t* status, cudaStream_t s) {
+  constexpr int kBins = 1 << BITS;
   uint32_t* keys[2] = {reinterpret_cast<uint32_t*>(ws + L.off_keys[0]),
                        reinterpret_cast<uint32_t*>(ws + L.off_keys[1])};
   uint32_t* perm[2] = {reinterpret_cast<uint32_t*>(ws + L.off_perm[0]),
@@ -324,23 +620,105 @@ cudaError_t launch_plan(const int64_t* rows, int64_t n, int64_t height, char* ws
   uint32_t* ghist = reinterpret_cast<uint32_t*>(ws + L.off_hist);
   uint32_t* tickets = reinterpret_cast<uint32_t*>(ws + L.off_tickets);
   uint32_t* lookback = reinterpret_cast<uint32_t*>(ws + L.off_lookback);
-  const int ni = static_cast<int>(n);
+  const size_t prep_smem = sizeof(uint32_t) * passes * kBins;
+  const size_t pass_smem = sizeof(uint32_t) * kBins + sizeof(uint16_t) * (kSortThreads / 32) * kBins;
+  cudaError_t e;
+  if (prep_smem > 48 * 1024) {
+    e = cudaFuncSetAttribute(k_prepare<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             static_cast<int>(prep_smem));
+    if (e != cudaSuccess) return e;
+  }
+  if (pass_smem > 48 * 1024) {
+    e = cudaFuncSetAttribute(k_radix_pass<BITS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             static_cast<int>(pass_smem));
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(k_radix_pass<BITS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             static_cast<int>(pass_smem));
+    if (e != cudaSuccess) return e;
+  }
   const int prep_grid = static_cast<int>(std::min<int64_t>(ceil_div(n, 256 * 4), 148 * 4));
-  k_prepare<<<prep_grid, 256, 0, s>>>(rows, ni, static_cast<uint32_t>(height), passes, keys[0],
-                                      ghist, status);
+  k_prepare<BITS><<<prep_grid, 256, prep_smem, s>>>(rows, n, height, passes, keys[0], ghist, status);
   const int tiles = static_cast<int>(L.sort_tiles);
   for (int p = 0; p < passes; ++p) {
-    uint32_t* st = lookback + static_cast<size_t>(p) * L.sort_tiles * kRadix;
+    uint32_t* st = lookback + static_cast<size_t>(p) * L.sort_tiles * kBins;
     if (p == 0)
-      k_radix_pass<false><<<tiles, kSortThreads, 0, s>>>(keys[0], nullptr, keys[1], perm[1], ni, 0,
-                                                         ghist, tickets + p, st);
+      k_radix_pass<BITS, false><<<tiles, kSortThreads, pass_smem, s>>>(
+          keys[0], nullptr, keys[1], perm[1], n, 0, ghist, tickets + p, st);
     else
-      k_radix_pass<true><<<tiles, kSortThreads, 0, s>>>(keys[p & 1], perm[p & 1], keys[(p + 1) & 1],
-                                                        perm[(p + 1) & 1], ni, p * kRadixBits,
-                                                        ghist + p * kRadix, tickets + p, st);
+      k_radix_pass<BITS, true><<<tiles, kSortThreads, pass_smem, s>>>(
+          keys[p & 1], perm[p & 1], keys[(p + 1) & 1], perm[(p + 1) & 1], n, p * BITS,
+          ghist + p * kBins, tickets + p, st);
   }
-  if (out) *out = plan_view(height, ws, L);
   return cudaGetLastError();
+}
+}  // namespace
+
+namespace {
+template <int BITS>
+cudaError_t launch_passes_direct(const int64_t* rows, int n, uint32_t height, int passes, char* ws,
+                                 const Workspace& L, int32_t* status, cudaStream_t s) {
+  constexpr int kBins = 1 << BITS;
+  uint32_t* keys[2] = {reinterpret_cast<uint32_t*>(ws + L.off_keys[0]),
+                       reinterpret_cast<uint32_t*>(ws + L.off_keys[1])};
+  uint32_t* perm[2] = {reinterpret_cast<uint32_t*>(ws + L.off_perm[0]),
+                       reinterpret_cast<uint32_t*>(ws + L.off_perm[1])};
+  uint32_t* hmat = reinterpret_cast<uint32_t*>(ws + L.off_lookback);
+  const int tiles = static_cast<int>(L.sort_tiles);
+  const size_t per_pass = static_cast<size_t>(tiles) * kBins;
+  k_prepare_direct<BITS><<<tiles, kSortThreads, 0, s>>>(rows, n, height, passes, keys[0], hmat, status);
+  for (int p = 0; p < passes; ++p) {
+    uint32_t* hn = p + 1 < passes ? hmat + (p + 1) * per_pass : nullptr;
+    if (p == 0)
+      k_radix_pass_direct<BITS, false><<<tiles, kSortThreads, 0, s>>>(
+          keys[0], nullptr, keys[1], perm[1], n, 0, hmat, hn);
+    else
+      k_radix_pass_direct<BITS, true><<<tiles, kSortThreads, 0, s>>>(
+          keys[p & 1], perm[p & 1], keys[(p + 1) & 1], perm[(p + 1) & 1], n, p * BITS,
+          hmat + p * per_pass, hn);
+  }
+  return cudaGetLastError();
+}
+}  // namespace
+
+cudaError_t launch_plan(const int64_t* rows, int64_t n, int64_t height, char* ws,
+                        const Workspace& L, int32_t* status, cudaStream_t s, SortedPlan* out) {
+  const DigitPlan dp = digit_plan(n, height);
+  // optional: the whole sort in one 16-CTA cluster launch (cluster_sort.cu).  Measured slower
+  // than the multi-launch path on B200, so it is opt-in.
+  static const bool use_cluster = std::getenv("B200EMB_CLUSTER_SORT") != nullptr;
+  if (use_cluster && cluster_sort_fits(n)) {
+    const int cpasses = static_cast<int>(ceil_div(key_bits(height), kRadixBits));
+    // the cluster kernel always uses 8-bit digits; it writes straight into the buffers the
+    // digit plan's parity selects
+    cudaError_t ce = launch_cluster_sort(
+        rows, n, height, cpasses, reinterpret_cast<uint32_t*>(ws + L.off_keys[dp.passes & 1]),
+        reinterpret_cast<uint32_t*>(ws + L.off_perm[dp.passes & 1]), status, s);
+    if (ce == cudaSuccess) {
+      if (out) *out = plan_view(n, height, ws, L);
+      return cudaSuccess;
+    }
+    if (ce != cudaErrorNotSupported) return ce;
+  }
+  const int ni = static_cast<int>(n);
+  const uint32_t h = static_cast<uint32_t>(height);
+  cudaError_t e;
+  if (dp.direct) {
+    switch (dp.bits) {
+      case 8: e = launch_passes_direct<8>(rows, ni, h, dp.passes, ws, L, status, s); break;
+      case 9: e = launch_passes_direct<9>(rows, ni, h, dp.passes, ws, L, status, s); break;
+      default: e = launch_passes_direct<10>(rows, ni, h, dp.passes, ws, L, status, s); break;
+    }
+  } else {
+    // only the words this plan uses need clearing
+    const size_t zero = L.off_lookback + sizeof(uint32_t) * static_cast<size_t>(dp.passes) *
+                                             L.sort_tiles * (1u << dp.bits);
+    e = cudaMemsetAsync(ws, 0, std::min(zero, L.zero_bytes), s);
+    if (e != cudaSuccess) return e;
+    e = launch_passes<8>(rows, ni, h, dp.passes, ws, L, status, s);
+  }
+  if (e != cudaSuccess) return e;
+  if (out) *out = plan_view(n, height, ws, L);
+  return cudaSuccess;
 }
 
 cudaError_t launch_head_scan(const SortedPlan& plan, int64_t n, uint32_t invalid_key, char* ws,

@@ -1,0 +1,43 @@
+// Developer tool: per-phase cycle stamps of the multi-launch radix sort plan.
+//   nvcc -O3 -std=c++20 -gencode arch=compute_100a,code=sm_100a -DB200EMB_PROFILE -o tools/sort_prof tools/sort_prof.cu
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+#include "../paddle-1_b200/csrc/sort.cu"
+namespace b200emb {
+bool cluster_sort_fits(int64_t) { return false; }
+cudaError_t launch_cluster_sort(const int64_t*, int64_t, int64_t, int, uint32_t*, uint32_t*, int32_t*, cudaStream_t) { return cudaErrorNotSupported; }
+}
+using namespace b200emb;
+int main(int argc, char** argv) {
+  const int n = argc > 1 ? atoi(argv[1]) : 106496;
+  const int64_t height = argc > 2 ? atoll(argv[2]) : 1000000;
+  std::vector<int64_t> h(n);
+  srand(1);
+  for (int i = 0; i < n; ++i) h[i] = (rand() % 8 == 0) ? 12345 : (static_cast<int64_t>(rand()) * 7919) % height;
+  Workspace L = make_workspace(n, 64, 4);
+  int64_t* d_rows; char* ws;
+  cudaMalloc(&d_rows, n * 8); cudaMalloc(&ws, L.total);
+  cudaMemcpy(d_rows, h.data(), n * 8, cudaMemcpyHostToDevice);
+  SortedPlan plan;
+  for (int it = 0; it < 3; ++it) launch_plan(d_rows, n, height, ws, L, nullptr, 0, &plan);
+  cudaDeviceSynchronize();
+  cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+  cudaEventRecord(e0);
+  for (int it = 0; it < 20; ++it) launch_plan(d_rows, n, height, ws, L, nullptr, 0, &plan);
+  cudaEventRecord(e1); cudaDeviceSynchronize();
+  float ms; cudaEventElapsedTime(&ms, e0, e1);
+  printf("n=%d passes=%d  %.2f us per plan (%s)\n", n, plan.passes, ms / 20 * 1e3, cudaGetErrorString(cudaGetLastError()));
+  static long long prof[256][8];
+  cudaMemcpyFromSymbol(prof, g_sort_prof, sizeof(prof));
+  const int tiles = (int)L.sort_tiles;
+  long long t0 = prof[0][0];
+  for (int t = 0; t < tiles && t < 256; ++t) if (prof[t][0] < t0) t0 = prof[t][0];
+  const char* names[] = {"load", "rank", "warp-reduce", "lookback", "ghist scan", "scatter"};
+  for (int t = 0; t < tiles && t < 256; t += (tiles > 16 ? tiles / 8 : 1)) {
+    printf("tile %3d start +%6lld:", t, prof[t][0] - t0);
+    for (int k = 0; k < 6; ++k) printf(" %s %lld", names[k], prof[t][k + 1] - prof[t][k]);
+    printf("  end +%lld\n", prof[t][6] - t0);
+  }
+  return 0;
+}
