@@ -43,6 +43,7 @@ extern "C" {
 #define B200EMB_E_WORKSPACE (-2)   /* workspace missing, misaligned or too small */
 #define B200EMB_E_CUDA (-3)        /* a CUDA call / launch failed (see b200emb_last_cuda_error) */
 #define B200EMB_E_UNSUPPORTED (-4) /* size beyond the documented limits */
+#define B200EMB_E_SCRATCH_LIMIT (-5) /* b200emb_sparse_sgd_noalloc_f32: request needs more than the built-in scratch */
 
 #define B200EMB_DETERMINISTIC 1u
 #define B200EMB_PLAN_READY 2u
@@ -145,6 +146,24 @@ int b200emb_sparse_adam_f64(double* param, double* moment1, double* moment2, int
                             float beta1, float beta2, float epsilon, void* workspace,
                             size_t workspace_bytes, unsigned flags, int32_t* status,
                             void* stream);
+
+/* Sparse SGD without a workspace argument — NO COUNTERPART IN THE REFERENCE (its kernels take
+ * temporaries from Fluid's allocator).  Same result as b200emb_sparse_sgd_f32; the scratch is a
+ * fixed array of B200EMB_NOALLOC_SCRATCH_BYTES inside the library's device image, so the call
+ * never allocates.  Meant for callers that hold nothing but the op's inputs and outputs and must
+ * not call cudaMalloc: thin FFI shims, processes whose framework pool already owns the GPU's
+ * memory, loops that cannot take cudaMalloc's device-wide sync.
+ *   - limit: b200emb_workspace_bytes(n, d, 4) must be <= B200EMB_NOALLOC_SCRATCH_BYTES (8 MiB; e.g.
+ *     131072 rows x 64 floats or 65536 x 128), otherwise B200EMB_E_SCRATCH_LIMIT and no launch;
+ *   - the array is shared by every call on the device and is not cleaned afterwards: calls that
+ *     may overlap on the GPU (other streams / threads) race — serialise them;
+ *   - the first call on each device resolves the array's device address
+ *     (cudaGetSymbolAddress); make that call before any stream capture;
+ *   - B200EMB_PLAN_READY is rejected (B200EMB_E_INVALID); B200EMB_DETERMINISTIC is honoured. */
+#define B200EMB_NOALLOC_SCRATCH_BYTES (8 * 1024 * 1024)
+int b200emb_sparse_sgd_noalloc_f32(float* param, int64_t height, int64_t d, const int64_t* rows,
+                                   const float* grad, int64_t n, const float* lr, unsigned flags,
+                                   int32_t* status, void* stream);
 
 #ifdef __cplusplus
 }

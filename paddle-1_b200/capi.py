@@ -15,7 +15,9 @@ DETERMINISTIC = 1
 PLAN_READY = 2
 
 _ERRORS = {-1: "invalid argument", -2: "workspace missing/misaligned/too small",
-           -3: "CUDA error", -4: "size beyond supported limits"}
+           -3: "CUDA error", -4: "size beyond supported limits",
+           -5: "request needs more than the library's built-in 8 MiB scratch"}
+NOALLOC_SCRATCH_BYTES = 8 * 1024 * 1024
 
 EXPORTS = [
     "b200emb_abi_version", "b200emb_last_cuda_error", "b200emb_workspace_bytes",
@@ -26,6 +28,7 @@ EXPORTS = [
     "b200emb_selected_rows_add_to_tensor_f32", "b200emb_selected_rows_add_to_tensor_f64",
     "b200emb_sparse_sgd_f32", "b200emb_sparse_sgd_f64",
     "b200emb_sparse_adam_f32", "b200emb_sparse_adam_f64",
+    "b200emb_sparse_sgd_noalloc_f32",
 ]
 
 _lib = None
@@ -223,4 +226,20 @@ def sparse_adam(param, moment1, moment2, rows, grad, lr, beta1_pow, beta2_pow, b
               ctypes.c_float(beta1), ctypes.c_float(beta2), ctypes.c_float(epsilon), _ptr(workspace),
               ctypes.c_size_t(workspace.numel()), ctypes.c_uint(flags), _ptr(status), _stream()),
            "sparse_adam")
+    return param
+
+
+def sparse_sgd_noalloc(param, rows, grad, lr, flags=0, status=None):
+    """In-place sparse SGD (float32) for callers that have no workspace to give and must not
+    allocate: the library's own fixed 8 MiB device array is the scratch.  Raises B200EmbError
+    when workspace_bytes(n, d) exceeds NOALLOC_SCRATCH_BYTES.  Calls on one device share that
+    array, so keep them on one stream (or otherwise serialised)."""
+    _need_cuda(param, rows, grad, lr, status)
+    if param.dtype != torch.float32:
+        raise TypeError("sparse_sgd_noalloc is float32 only")
+    n = rows.numel()
+    v, d = param.shape
+    _check(lib().b200emb_sparse_sgd_noalloc_f32(
+        _ptr(param), ctypes.c_int64(v), ctypes.c_int64(d), _ptr(rows), _ptr(grad), ctypes.c_int64(n),
+        _ptr(lr), ctypes.c_uint(flags), _ptr(status), _stream()), "sparse_sgd_noalloc")
     return param
