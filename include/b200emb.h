@@ -92,6 +92,38 @@ int b200emb_selected_rows_add_to(const int64_t* in_rows, const void* in_value, i
 int b200emb_plan_rows(const int64_t* rows, int64_t n, int64_t height, void* workspace,
                       size_t workspace_bytes, int32_t* status, void* stream);
 
+/* Sharded lookup plan (K6) — the device-side counterpart of the reference's CPU-only split_ids op
+ * (operators/split_ids_op.h:36-58, `PADDLE_THROW` on GPU at :30-32): owner(id) = id % num_shards,
+ * local row = id / num_shards.  Sorts rows by key = owner * ceil(height/num_shards) + local row and
+ * de-duplicates them:
+ *   unique_keys[0..U)  ascending unique keys (must hold n entries), *n_unique = U (device int64),
+ *   shard_bounds[g]    (nullable, num_shards+1 entries) first unique index owned by shard g,
+ *   elem_bounds[g]     (nullable, num_shards+1 entries) first position, in plan order, owned by shard g,
+ *   local_rows[0..U)   (nullable) key % shard_height = the row inside the owner's shard.
+ * The workspace then holds the plan (keys, positions, unique index): run merge_add / sparse_* on the
+ * same rows with B200EMB_PLAN_READY and height = plan_height = num_shards*ceil(height/num_shards)
+ * (= height when num_shards == 1) to reduce in exactly this order. */
+int b200emb_plan_unique_rows(const int64_t* rows, int64_t n, int64_t height, int64_t num_shards,
+                             int64_t* unique_keys, int64_t* n_unique, int64_t* shard_bounds,
+                             int64_t* elem_bounds, int64_t* local_rows, void* workspace,
+                             size_t workspace_bytes, int32_t* status, void* stream);
+
+/* Inverse of the de-duplication — the device-side merge_ids (operators/merge_ids_op.h:63-87,
+ * CPU-only in the reference): out[i,:] = unique_values[u(i),:] where u(i) is the unique index of
+ * rows[i] in the plan held by `workspace` (b200emb_plan_unique_rows). */
+int b200emb_expand_unique_f32(const float* unique_values, int64_t n, int64_t d, int64_t plan_height,
+                              void* workspace, size_t workspace_bytes, float* out, void* stream);
+int b200emb_expand_unique_f64(const double* unique_values, int64_t n, int64_t d, int64_t plan_height,
+                              void* workspace, size_t workspace_bytes, double* out, void* stream);
+
+/* out[e,:] = value[position of the e-th id in plan order,:] — rows of a [n,d] block reordered into
+ * the plan's (owner, local row, original position) order; used to ship un-merged gradient rows
+ * in the bit-exact mode (split_ids on a SelectedRows, operators/split_ids_op.h:59-92). */
+int b200emb_gather_sorted_f32(const float* value, int64_t n, int64_t d, int64_t plan_height,
+                              void* workspace, size_t workspace_bytes, float* out, void* stream);
+int b200emb_gather_sorted_f64(const double* value, int64_t n, int64_t d, int64_t plan_height,
+                              void* workspace, size_t workspace_bytes, double* out, void* stream);
+
 /* scatter::MergeAdd — replaces math/selected_rows_functor.cu:235-297 (CPU semantics
  * selected_rows_functor.cc:193-228): out_rows = ascending unique rows, out_value[u,:] = sum of
  * the input rows with that id.  out_rows/out_value must hold n rows; *n_unique (device int64)

@@ -29,6 +29,8 @@ EXPORTS = [
     "b200emb_sparse_sgd_f32", "b200emb_sparse_sgd_f64",
     "b200emb_sparse_adam_f32", "b200emb_sparse_adam_f64",
     "b200emb_sparse_sgd_noalloc_f32",
+    "b200emb_plan_unique_rows", "b200emb_expand_unique_f32", "b200emb_expand_unique_f64",
+    "b200emb_gather_sorted_f32", "b200emb_gather_sorted_f64",
 ]
 
 _lib = None
@@ -105,6 +107,13 @@ def workspace_bytes(n, d, elem_size=4):
 
 def alloc_workspace(n, d, elem_size=4, device="cuda"):
     nbytes = max(workspace_bytes(n, d, elem_size), 256)
+    return torch.empty(nbytes, dtype=torch.uint8, device=device)
+
+
+def alloc_workspace_upto(n_max, d, elem_size=4, device="cuda"):
+    """Workspace valid for ANY n <= n_max (the layout switches sort modes at 131 072 ids, so the
+    requirement is not monotonic across that boundary)."""
+    nbytes = max(workspace_bytes(n_max, d, elem_size), workspace_bytes(min(n_max, 131072), d, elem_size), 256)
     return torch.empty(nbytes, dtype=torch.uint8, device=device)
 
 
@@ -243,3 +252,54 @@ def sparse_sgd_noalloc(param, rows, grad, lr, flags=0, status=None):
         _ptr(param), ctypes.c_int64(v), ctypes.c_int64(d), _ptr(rows), _ptr(grad), ctypes.c_int64(n),
         _ptr(lr), ctypes.c_uint(flags), _ptr(status), _stream()), "sparse_sgd_noalloc")
     return param
+
+
+def plan_height(height, num_shards):
+    """Height the plan is built for: num_shards * ceil(height / num_shards) (= height for one shard)."""
+    if num_shards <= 1:
+        return int(height)
+    return int(num_shards) * ((int(height) + num_shards - 1) // num_shards)
+
+
+def plan_unique_rows(rows, height, num_shards, workspace, status=None, want_elem_bounds=False):
+    """Sort rows by (owner = id % num_shards, local row = id // num_shards) and de-duplicate.
+
+    Returns (unique_keys[n], n_unique[1], shard_bounds[num_shards+1], elem_bounds or None, local_rows[n]);
+    only the first U entries of unique_keys / local_rows are meaningful.  The workspace keeps the plan."""
+    _need_cuda(rows, workspace, status)
+    n = rows.numel()
+    dev = rows.device
+    ukeys = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
+    local = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
+    n_unique = torch.zeros(1, dtype=torch.int64, device=dev)
+    bounds = torch.zeros(num_shards + 1, dtype=torch.int64, device=dev)
+    ebounds = torch.zeros(num_shards + 1, dtype=torch.int64, device=dev) if want_elem_bounds else None
+    _check(lib().b200emb_plan_unique_rows(
+        _ptr(rows), ctypes.c_int64(n), ctypes.c_int64(height), ctypes.c_int64(num_shards), _ptr(ukeys),
+        _ptr(n_unique), _ptr(bounds), _ptr(ebounds), _ptr(local), _ptr(workspace),
+        ctypes.c_size_t(workspace.numel()), _ptr(status), _stream()), "plan_unique_rows")
+    return ukeys, n_unique, bounds, ebounds, local
+
+
+def _permute(name, src, n, d, plan_h, workspace, out):
+    _need_cuda(src, workspace, out)
+    fn = getattr(lib(), name + _sfx(src.dtype))
+    _check(fn(_ptr(src), ctypes.c_int64(n), ctypes.c_int64(d), ctypes.c_int64(plan_h), _ptr(workspace),
+              ctypes.c_size_t(workspace.numel()), _ptr(out), _stream()), name)
+    return out
+
+
+def expand_unique(unique_values, n, plan_h, workspace, out=None):
+    """out[i,:] = unique_values[unique index of rows[i], :] for the plan held by `workspace`."""
+    d = unique_values.shape[1]
+    if out is None:
+        out = torch.empty((n, d), dtype=unique_values.dtype, device=unique_values.device)
+    return _permute("b200emb_expand_unique_", unique_values, n, d, plan_h, workspace, out)
+
+
+def gather_sorted(value, plan_h, workspace, out=None):
+    """Rows of value[n,d] reordered into the plan's (owner, local row, position) order."""
+    n, d = value.shape
+    if out is None:
+        out = torch.empty_like(value)
+    return _permute("b200emb_gather_sorted_", value, n, d, plan_h, workspace, out)

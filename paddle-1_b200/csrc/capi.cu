@@ -156,6 +156,86 @@ int b200emb_plan_rows(const int64_t* rows, int64_t n, int64_t height, void* work
   return e == cudaSuccess ? B200EMB_OK : fail_cuda(e);
 }
 
+int b200emb_plan_unique_rows(const int64_t* rows, int64_t n, int64_t height, int64_t num_shards,
+                             int64_t* unique_keys, int64_t* n_unique, int64_t* shard_bounds,
+                             int64_t* elem_bounds, int64_t* local_rows, void* workspace,
+                             size_t workspace_bytes, int32_t* status, void* stream) {
+  int rc = check_sizes(n, 1, height);
+  if (rc != B200EMB_OK) return rc;
+  if (num_shards < 1 || num_shards > 65536) return B200EMB_E_INVALID;
+  const int64_t shard_height = ceil_div(height, num_shards);
+  const int64_t plan_height = num_shards > 1 ? num_shards * shard_height : height;
+  if (plan_height >= 0xFFFFFFFFLL) return B200EMB_E_UNSUPPORTED;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (!n_unique || (n > 0 && (!rows || !unique_keys))) return B200EMB_E_INVALID;
+  if (n == 0) {
+    cudaError_t e = cudaMemsetAsync(n_unique, 0, sizeof(int64_t), s);
+    if (e == cudaSuccess && shard_bounds)
+      e = cudaMemsetAsync(shard_bounds, 0, sizeof(int64_t) * (num_shards + 1), s);
+    if (e == cudaSuccess && elem_bounds)
+      e = cudaMemsetAsync(elem_bounds, 0, sizeof(int64_t) * (num_shards + 1), s);
+    return e == cudaSuccess ? B200EMB_OK : fail_cuda(e);
+  }
+  const Workspace L = make_workspace(n, 1, 4);
+  rc = check_workspace(workspace, workspace_bytes, L);
+  if (rc != B200EMB_OK) return rc;
+  char* ws = static_cast<char*>(workspace);
+  KeyMap km;
+  km.shards = static_cast<uint32_t>(num_shards);
+  km.shard_height = static_cast<uint32_t>(shard_height);
+  km.raw_height = static_cast<uint32_t>(height);
+  SortedPlan plan;
+  cudaError_t e = launch_plan(rows, n, plan_height, ws, L, status, s, &plan, &km);
+  if (e != cudaSuccess) return fail_cuda(e);
+  e = launch_head_scan(plan, n, static_cast<uint32_t>(plan_height), ws, L, unique_keys, n_unique, s);
+  if (e != cudaSuccess) return fail_cuda(e);
+  if (shard_bounds || elem_bounds || local_rows) {
+    e = launch_shard_split(unique_keys, plan, ws, L, static_cast<int>(num_shards),
+                           static_cast<uint32_t>(num_shards > 1 ? shard_height : plan_height), n,
+                           static_cast<uint32_t>(plan_height), shard_bounds, elem_bounds, local_rows, s);
+    if (e != cudaSuccess) return fail_cuda(e);
+  }
+  return B200EMB_OK;
+}
+
+extern "C++" {
+namespace {
+template <typename T>
+int run_permute(const T* src, int64_t n, int64_t d, int64_t plan_height, void* workspace,
+                size_t workspace_bytes, T* out, bool unique, void* stream) {
+  int rc = check_sizes(n, d, plan_height);
+  if (rc != B200EMB_OK) return rc;
+  if (n == 0) return B200EMB_OK;
+  if (!src || !out) return B200EMB_E_INVALID;
+  const Workspace L = make_workspace(n, 1, 4);
+  rc = check_workspace(workspace, workspace_bytes, L);
+  if (rc != B200EMB_OK) return rc;
+  char* ws = static_cast<char*>(workspace);
+  const SortedPlan plan = plan_view(n, plan_height, ws, L);
+  cudaError_t e = launch_permute_rows<T>(src, plan, reinterpret_cast<const uint32_t*>(ws + L.off_uidx), n,
+                                         d, out, unique, static_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? B200EMB_OK : fail_cuda(e);
+}
+}  // namespace
+}  // extern "C++"
+
+int b200emb_expand_unique_f32(const float* unique_values, int64_t n, int64_t d, int64_t plan_height,
+                              void* workspace, size_t workspace_bytes, float* out, void* stream) {
+  return run_permute<float>(unique_values, n, d, plan_height, workspace, workspace_bytes, out, true, stream);
+}
+int b200emb_expand_unique_f64(const double* unique_values, int64_t n, int64_t d, int64_t plan_height,
+                              void* workspace, size_t workspace_bytes, double* out, void* stream) {
+  return run_permute<double>(unique_values, n, d, plan_height, workspace, workspace_bytes, out, true, stream);
+}
+int b200emb_gather_sorted_f32(const float* value, int64_t n, int64_t d, int64_t plan_height,
+                              void* workspace, size_t workspace_bytes, float* out, void* stream) {
+  return run_permute<float>(value, n, d, plan_height, workspace, workspace_bytes, out, false, stream);
+}
+int b200emb_gather_sorted_f64(const double* value, int64_t n, int64_t d, int64_t plan_height,
+                              void* workspace, size_t workspace_bytes, double* out, void* stream) {
+  return run_permute<double>(value, n, d, plan_height, workspace, workspace_bytes, out, false, stream);
+}
+
 #define B200EMB_DEFINE_UPDATES(T, S)                                                             \
   int b200emb_merge_add_##S(const int64_t* rows, const T* value, int64_t n, int64_t d,           \
                             int64_t height, int64_t* out_rows, T* out_value, int64_t* n_unique,  \

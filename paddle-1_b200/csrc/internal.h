@@ -59,9 +59,25 @@ struct SortedPlan {      // device pointers into the workspace after plan_rows
   int passes;
 };
 
+// Optional id -> sort-key remapping applied while narrowing ids to 32 bits.  With `shards` > 1 the
+// key is (id % shards) * shard_height + id / shards: the owner convention of the reference's
+// split_ids op (operators/split_ids_op.h:45-49), so one sort groups ids by owning shard and, inside
+// a shard, by local row.  `raw_height` bounds the incoming ids; the plan's height is then
+// shards * shard_height.
+struct KeyMap {
+  uint32_t shards = 1, shard_height = 0, raw_height = 0;
+#if defined(__CUDACC__)
+  __host__ __device__
+#endif
+  uint32_t operator()(uint32_t id) const {
+    return shards > 1 ? (id % shards) * shard_height + id / shards : id;
+  }
+};
+
 // sort.cu
 cudaError_t launch_plan(const int64_t* rows, int64_t n, int64_t height, char* ws,
-                        const Workspace& L, int32_t* status, cudaStream_t s, SortedPlan* out);
+                        const Workspace& L, int32_t* status, cudaStream_t s, SortedPlan* out,
+                        const KeyMap* keymap = nullptr);
 SortedPlan plan_view(int64_t n, int64_t height, char* ws, const Workspace& L);
 cudaError_t launch_head_scan(const SortedPlan& plan, int64_t n, uint32_t invalid_key, char* ws,
                              const Workspace& L, int64_t* out_rows, int64_t* n_unique_out,
@@ -98,5 +114,14 @@ cudaError_t launch_update(const SortedPlan& plan, const T* value, int64_t n, int
                           const Workspace& L, int32_t* status, cudaStream_t s);
 
 int choose_chunk(int64_t n, int groups_per_sm);
+
+// shard.cu
+cudaError_t launch_shard_split(const int64_t* ukeys, const SortedPlan& plan, char* ws,
+                               const Workspace& L, int shards, uint32_t shard_height, int64_t n,
+                               uint32_t invalid_key, int64_t* bounds, int64_t* elem_bounds,
+                               int64_t* local_rows, cudaStream_t s);
+template <typename T>
+cudaError_t launch_permute_rows(const T* src, const SortedPlan& plan, const uint32_t* uidx, int64_t n,
+                                int64_t d, T* out, bool unique, cudaStream_t s);
 
 }  // namespace b200emb

@@ -154,7 +154,7 @@ __device__ __forceinline__ void look_back_vec(const uint32_t* state, int tile, s
 // for small N where every pass saved is a launch + chained scan saved.
 template <int BITS>
 __global__ void __launch_bounds__(256)
-k_prepare(const int64_t* __restrict__ rows, int n, uint32_t height, int passes,
+k_prepare(const int64_t* __restrict__ rows, int n, uint32_t height, KeyMap km, int passes,
           uint32_t* __restrict__ keys, uint32_t* __restrict__ ghist, int32_t* status) {
   constexpr int kBins = 1 << BITS;
   extern __shared__ uint32_t sh[];   // [passes][kBins]
@@ -169,8 +169,8 @@ k_prepare(const int64_t* __restrict__ rows, int n, uint32_t height, int passes,
     uint32_t key = 0;
     if (valid) {
       const int64_t r = rows[i];
-      const bool ok = r >= 0 && r < static_cast<int64_t>(height);
-      key = ok ? static_cast<uint32_t>(r) : height;  // out-of-range rows sort last
+      const bool ok = r >= 0 && r < static_cast<int64_t>(km.raw_height);
+      key = ok ? km(static_cast<uint32_t>(r)) : height;  // out-of-range rows sort last
       bad |= !ok;
       keys[i] = key;
     }
@@ -317,7 +317,7 @@ constexpr int kDirectMaxTiles = 64;
 
 template <int BITS>
 __global__ void __launch_bounds__(kSortThreads)
-k_prepare_direct(const int64_t* __restrict__ rows, int n, uint32_t height, int passes,
+k_prepare_direct(const int64_t* __restrict__ rows, int n, uint32_t height, KeyMap km, int passes,
                  uint32_t* __restrict__ keys, uint32_t* __restrict__ hmat, int32_t* status) {
   constexpr int kBins = 1 << BITS;
   __shared__ uint32_t sh[kBins];
@@ -333,8 +333,8 @@ k_prepare_direct(const int64_t* __restrict__ rows, int n, uint32_t height, int p
     uint32_t key = 0;
     if (valid) {
       const int64_t r = rows[i];
-      const bool ok = r >= 0 && r < static_cast<int64_t>(height);
-      key = ok ? static_cast<uint32_t>(r) : height;
+      const bool ok = r >= 0 && r < static_cast<int64_t>(km.raw_height);
+      key = ok ? km(static_cast<uint32_t>(r)) : height;
       bad |= !ok;
       keys[i] = key;
     }
@@ -610,8 +610,8 @@ SortedPlan plan_view(int64_t n, int64_t height, char* ws, const Workspace& L) {
 
 namespace {
 template <int BITS>
-cudaError_t launch_passes(const int64_t* rows, int n, uint32_t height, int passes, char* ws,
-                          const Workspace& L, int32_t* status, cudaStream_t s) {
+cudaError_t launch_passes(const int64_t* rows, int n, uint32_t height, KeyMap km, int passes,
+                          char* ws, const Workspace& L, int32_t* status, cudaStream_t s) {
   constexpr int kBins = 1 << BITS;
   uint32_t* keys[2] = {reinterpret_cast<uint32_t*>(ws + L.off_keys[0]),
                        reinterpret_cast<uint32_t*>(ws + L.off_keys[1])};
@@ -637,7 +637,7 @@ cudaError_t launch_passes(const int64_t* rows, int n, uint32_t height, int passe
     if (e != cudaSuccess) return e;
   }
   const int prep_grid = static_cast<int>(std::min<int64_t>(ceil_div(n, 256 * 4), 148 * 4));
-  k_prepare<BITS><<<prep_grid, 256, prep_smem, s>>>(rows, n, height, passes, keys[0], ghist, status);
+  k_prepare<BITS><<<prep_grid, 256, prep_smem, s>>>(rows, n, height, km, passes, keys[0], ghist, status);
   const int tiles = static_cast<int>(L.sort_tiles);
   for (int p = 0; p < passes; ++p) {
     uint32_t* st = lookback + static_cast<size_t>(p) * L.sort_tiles * kBins;
@@ -655,8 +655,8 @@ cudaError_t launch_passes(const int64_t* rows, int n, uint32_t height, int passe
 
 namespace {
 template <int BITS>
-cudaError_t launch_passes_direct(const int64_t* rows, int n, uint32_t height, int passes, char* ws,
-                                 const Workspace& L, int32_t* status, cudaStream_t s) {
+cudaError_t launch_passes_direct(const int64_t* rows, int n, uint32_t height, KeyMap km, int passes,
+                                 char* ws, const Workspace& L, int32_t* status, cudaStream_t s) {
   constexpr int kBins = 1 << BITS;
   uint32_t* keys[2] = {reinterpret_cast<uint32_t*>(ws + L.off_keys[0]),
                        reinterpret_cast<uint32_t*>(ws + L.off_keys[1])};
@@ -665,7 +665,7 @@ cudaError_t launch_passes_direct(const int64_t* rows, int n, uint32_t height, in
   uint32_t* hmat = reinterpret_cast<uint32_t*>(ws + L.off_lookback);
   const int tiles = static_cast<int>(L.sort_tiles);
   const size_t per_pass = static_cast<size_t>(tiles) * kBins;
-  k_prepare_direct<BITS><<<tiles, kSortThreads, 0, s>>>(rows, n, height, passes, keys[0], hmat, status);
+  k_prepare_direct<BITS><<<tiles, kSortThreads, 0, s>>>(rows, n, height, km, passes, keys[0], hmat, status);
   for (int p = 0; p < passes; ++p) {
     uint32_t* hn = p + 1 < passes ? hmat + (p + 1) * per_pass : nullptr;
     if (p == 0)
@@ -681,12 +681,16 @@ cudaError_t launch_passes_direct(const int64_t* rows, int n, uint32_t height, in
 }  // namespace
 
 cudaError_t launch_plan(const int64_t* rows, int64_t n, int64_t height, char* ws,
-                        const Workspace& L, int32_t* status, cudaStream_t s, SortedPlan* out) {
+                        const Workspace& L, int32_t* status, cudaStream_t s, SortedPlan* out,
+                        const KeyMap* keymap) {
+  KeyMap km;
+  km.raw_height = static_cast<uint32_t>(height);
+  if (keymap) km = *keymap;
   const DigitPlan dp = digit_plan(n, height);
   // optional: the whole sort in one 16-CTA cluster launch (cluster_sort.cu).  Measured slower
   // than the multi-launch path on B200, so it is opt-in.
   static const bool use_cluster = std::getenv("B200EMB_CLUSTER_SORT") != nullptr;
-  if (use_cluster && cluster_sort_fits(n)) {
+  if (use_cluster && km.shards <= 1 && cluster_sort_fits(n)) {
     const int cpasses = static_cast<int>(ceil_div(key_bits(height), kRadixBits));
     // the cluster kernel always uses 8-bit digits; it writes straight into the buffers the
     // digit plan's parity selects
@@ -704,9 +708,9 @@ cudaError_t launch_plan(const int64_t* rows, int64_t n, int64_t height, char* ws
   cudaError_t e;
   if (dp.direct) {
     switch (dp.bits) {
-      case 8: e = launch_passes_direct<8>(rows, ni, h, dp.passes, ws, L, status, s); break;
-      case 9: e = launch_passes_direct<9>(rows, ni, h, dp.passes, ws, L, status, s); break;
-      default: e = launch_passes_direct<10>(rows, ni, h, dp.passes, ws, L, status, s); break;
+      case 8: e = launch_passes_direct<8>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
+      case 9: e = launch_passes_direct<9>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
+      default: e = launch_passes_direct<10>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
     }
   } else {
     // only the words this plan uses need clearing
@@ -714,7 +718,7 @@ cudaError_t launch_plan(const int64_t* rows, int64_t n, int64_t height, char* ws
                                              L.sort_tiles * (1u << dp.bits);
     e = cudaMemsetAsync(ws, 0, std::min(zero, L.zero_bytes), s);
     if (e != cudaSuccess) return e;
-    e = launch_passes<8>(rows, ni, h, dp.passes, ws, L, status, s);
+    e = launch_passes<8>(rows, ni, h, km, dp.passes, ws, L, status, s);
   }
   if (e != cudaSuccess) return e;
   if (out) *out = plan_view(n, height, ws, L);

@@ -1,0 +1,158 @@
+"""GPU tests of the sharded-path kernels (csrc/shard.cu + key-mapped sort plan) through the C ABI,
+and of ShardedTable on the CUDA backend: world 1 always, world 2 over NCCL when two GPUs exist."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+import oracle
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+@pytest.fixture(scope="module")
+def capi(pkg):
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    pkg.capi.lib()
+    return pkg.capi
+
+
+def _zipf_ids(rng, n, v):
+    w = np.arange(1, v + 1, dtype=np.float64) ** -1.1
+    cdf = np.cumsum(w) / w.sum()
+    return ((np.searchsorted(cdf, rng.random(n)) * 2654435761 + 12345) % v).astype(np.int64)
+
+
+@pytest.mark.parametrize("n,v,shards", [(5000, 777, 1), (5000, 1003, 4), (150000, 100000, 8), (300000, 4000000, 3)])
+def test_plan_unique_rows_matches_split_ids_semantics(capi, n, v, shards):
+    from sharded_cpu_ops import CpuCheckerOps, _Plan
+    rng = np.random.default_rng(n + shards)
+    ids = _zipf_ids(rng, n, v)
+    ids[::97] = v + 5            # a few out-of-range ids: flagged and dropped
+    d_ids = torch.from_numpy(ids).cuda()
+    ws = capi.alloc_workspace(n, 8)
+    status = capi.new_status()
+    ukeys, nu, bounds, eb, local = capi.plan_unique_rows(d_ids, v, shards, ws, status=status, want_elem_bounds=True)
+    plan = _Plan()
+    wk, wn, wb, web, wl = CpuCheckerOps().plan_unique(torch.from_numpy(ids), v, shards, plan, True)
+    u = int(nu.item())
+    assert u == int(wn.item()) and int(status.item()) & 2
+    assert np.array_equal(ukeys.cpu().numpy()[:u], wk.numpy()[:u])
+    assert np.array_equal(local.cpu().numpy()[:u], wl.numpy()[:u])
+    assert bounds.cpu().tolist() == wb.tolist()
+    assert eb.cpu().tolist() == web.tolist()
+    # owner of every unique key agrees with the reference's id % shard_num
+    hs = (v + shards - 1) // shards
+    if shards > 1:
+        gids = local.cpu().numpy()[:u] * shards + ukeys.cpu().numpy()[:u] // hs
+        assert np.array_equal(np.sort(gids), np.unique(ids[ids < v]))
+        per_owner = oracle.split_ids(np.unique(ids[ids < v]), shards)
+        b = bounds.cpu().numpy()
+        for g in range(shards):
+            assert b[g + 1] - b[g] == len(per_owner[g])
+    # expand (merge_ids) and gather_sorted against numpy on the same plan
+    ph = capi.plan_height(v, shards)
+    uvals = torch.from_numpy(rng.standard_normal((max(u, 1), 8)).astype(np.float32)).cuda()
+    got = capi.expand_unique(uvals, n, ph, ws).cpu().numpy()
+    valid = ids < v
+    want = uvals.cpu().numpy()[np.minimum(plan.uidx, max(u, 1) - 1)][np.argsort(plan.perm, kind="stable")]
+    assert np.array_equal(got[valid], want[valid])
+    val = torch.from_numpy(rng.standard_normal((n, 8)).astype(np.float32)).cuda()
+    assert np.array_equal(capi.gather_sorted(val, ph, ws).cpu().numpy(), val.cpu().numpy()[plan.perm])
+
+
+@pytest.mark.parametrize("deterministic", [True, False], ids=["bit-exact", "fast"])
+def test_sharded_table_world1_cuda(capi, pkg, deterministic):
+    v, d, n = 50000, 64, 30000
+    rng = np.random.default_rng(5)
+    full = (rng.random((v, d)) * 0.1 - 0.05).astype(np.float32)
+    ids = _zipf_ids(rng, n, v)
+    dout = (rng.standard_normal((n, d)) * 0.01).astype(np.float32)
+    tab = pkg.sharded.ShardedTable(v, d, pkg.sharded.CudaOps(capi), torch.device("cuda"),
+                                   init=lambda rows: torch.from_numpy(full[rows.numpy()]))
+    ws = capi.alloc_workspace(n, d)
+    out, ctx = tab.lookup(torch.from_numpy(ids).cuda(), ws, deterministic=deterministic)
+    assert np.array_equal(out.cpu().numpy(), full[ids])
+    lr = torch.tensor([0.05], device="cuda")
+    tab.update(ctx, torch.from_numpy(dout).cuda(), lr, deterministic=deterministic)
+    after = tab.gather_full_table().cpu().numpy()
+    want = full.copy()
+    oracle.sgd_sparse(want, ids, dout, np.array([0.05], np.float32))
+    if deterministic:
+        assert np.array_equal(after.view(np.uint32), want.view(np.uint32))
+    else:
+        rows, merged = oracle.merge_add(ids, dout, truth=True)
+        truth = full.astype(np.float64)
+        truth[rows] -= 0.05 * merged
+        _, l1 = oracle.merge_add(ids, np.abs(dout), truth=True)
+        bound = 1e-6 * np.abs(full)
+        bound[rows] += 1e-6 * 0.05 * l1
+        assert (np.abs(after - truth) <= bound + 1e-30).all()
+
+
+def _nccl_worker(rank, world, port, deterministic, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    import torch.distributed as dist
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world)
+    try:
+        import __graft_entry__ as ge
+        pkg = ge.load_package()
+        v, d, n = 200003, 64, 60000
+        full = (np.random.default_rng(7).random((v, d)) * 0.1 - 0.05).astype(np.float32)
+        rng = np.random.default_rng(100 + rank)
+        ids = _zipf_ids(rng, n, v)
+        dout = (rng.standard_normal((n, d)) * 0.01).astype(np.float32)
+        dev = torch.device("cuda", rank)
+        tab = pkg.sharded.ShardedTable(v, d, pkg.sharded.CudaOps(pkg.capi), dev,
+                                       init=lambda rows: torch.from_numpy(full[rows.numpy()]))
+        ws = pkg.capi.alloc_workspace(n, d, 4, dev)
+        out, ctx = tab.lookup(torch.from_numpy(ids).to(dev), ws, deterministic=deterministic)
+        ok = np.array_equal(out.cpu().numpy(), full[ids])
+        tab.update(ctx, torch.from_numpy(dout).to(dev), torch.tensor([0.05], device=dev), deterministic=deterministic)
+        after = tab.gather_full_table().cpu().numpy()
+        q.put((rank, ok, after if rank == 0 else None, ids, dout))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("deterministic", [True, False], ids=["bit-exact", "fast"])
+def test_sharded_table_two_gpus_nccl(capi, deterministic):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_nccl_worker, args=(r, 2, port, deterministic, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = sorted([q.get(timeout=300) for _ in range(2)], key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(g[1] for g in got)
+    v, d = 200003, 64
+    want = (np.random.default_rng(7).random((v, d)) * 0.1 - 0.05).astype(np.float32)
+    base = want.copy()
+    ids = np.concatenate([g[3] for g in got])
+    dout = np.concatenate([g[4] for g in got])
+    after = got[0][2]
+    if deterministic:
+        oracle.sgd_sparse(want, ids, dout, np.array([0.05], np.float32))
+        assert np.array_equal(after.view(np.uint32), want.view(np.uint32))
+    else:
+        rows, merged = oracle.merge_add(ids, dout, truth=True)
+        truth = base.astype(np.float64)
+        truth[rows] -= 0.05 * merged
+        _, l1 = oracle.merge_add(ids, np.abs(dout), truth=True)
+        bound = 1e-6 * np.abs(base)
+        bound[rows] += 1e-6 * 0.05 * l1
+        assert (np.abs(after - truth) <= bound + 1e-30).all()
