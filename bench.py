@@ -377,6 +377,8 @@ def main():
     ap.add_argument("--steps", type=int, default=400)
     ap.add_argument("--warmup", type=int, default=40)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--ids-per-gpu", type=int, default=0, dest="ids_per_gpu",
+                    help="sharded runs: ids per GPU per step (default 16 x 4096 x 26)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":

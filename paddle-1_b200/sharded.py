@@ -90,6 +90,26 @@ def all_to_all_rows(out, inp, out_splits, in_splits, group=None):
         r.wait()
 
 
+class _Phase:
+    """with table._phase("name"): ... records a CUDA-event pair when table.phase_events is a list."""
+
+    def __init__(self, table, name):
+        self.t, self.name = table, name
+
+    def __enter__(self):
+        if self.t.phase_events is not None:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+        return self
+
+    def __exit__(self, *exc):
+        if self.t.phase_events is not None:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            self.t.phase_events.append((self.name, self.e0, e1))
+        return False
+
+
 class ShardedTable:
     """This rank's shard of a [height, d] table plus the exchange logic of one training step."""
 
@@ -110,32 +130,42 @@ class ShardedTable:
             self.m1 = torch.zeros_like(self.shard)
             self.m2 = torch.zeros_like(self.shard)
         self.bytes_sent = 0
+        self.phase_events = None      # set to [] to record (name, start_event, end_event) per phase
+
+    def _phase(self, name):
+        return _Phase(self, name)
 
     # ------------------------------------------------------------------ forward
     def lookup(self, ids, ws, deterministic=False):
         """ids: int64 [n] on this rank.  Returns (out [n, d], ctx for update())."""
         n = ids.numel()
-        ukeys, n_unique, bounds, ebounds, local = self.ops.plan_unique(ids, self.height, self.world, ws,
-                                                                       deterministic)
+        with self._phase("plan+dedup"):
+            ukeys, n_unique, bounds, ebounds, local = self.ops.plan_unique(ids, self.height, self.world, ws,
+                                                                           deterministic)
         # split sizes of every rank in one collective + one host read
         mine = bounds if ebounds is None else torch.cat([bounds, ebounds])
-        if self.world > 1:
-            gathered = [torch.empty_like(mine) for _ in range(self.world)]
-            dist.all_gather(gathered, mine, group=self.group)
-            table = torch.stack(gathered).cpu()
-        else:
-            table = mine.reshape(1, -1).cpu()
+        with self._phase("split sizes (all_gather + host read)"):
+            if self.world > 1:
+                gathered = [torch.empty_like(mine) for _ in range(self.world)]
+                dist.all_gather(gathered, mine, group=self.group)
+                table = torch.stack(gathered).cpu()
+            else:
+                table = mine.reshape(1, -1).cpu()
         g1 = self.world + 1
         ub = table[:, :g1]
         send = (ub[self.rank, 1:] - ub[self.rank, :-1]).tolist()
         recv = (ub[:, self.rank + 1] - ub[:, self.rank]).tolist()
         u = int(ub[self.rank, self.world])
         recv_local = torch.empty(sum(recv), dtype=torch.int64, device=ids.device)
-        all_to_all_rows(recv_local, local[:u], recv, send, self.group)
-        rows = self.ops.lookup(self.shard, recv_local)
+        with self._phase("id all-to-all"):
+            all_to_all_rows(recv_local, local[:u], recv, send, self.group)
+        with self._phase("owner gather"):
+            rows = self.ops.lookup(self.shard, recv_local)
         uvals = torch.empty((u, self.d), dtype=self.dtype, device=ids.device)
-        all_to_all_rows(uvals, rows, send, recv, self.group)
-        out = self.ops.expand_unique(uvals, n, self.plan_h, ws)
+        with self._phase("row all-to-all"):
+            all_to_all_rows(uvals, rows, send, recv, self.group)
+        with self._phase("expand to batch order"):
+            out = self.ops.expand_unique(uvals, n, self.plan_h, ws)
         self.bytes_sent += (u - send[self.rank]) * 8 + (sum(recv) - recv[self.rank]) * self.d * rows.element_size()
         ctx = {"ids": ids, "n": n, "u": u, "send": send, "recv": recv, "recv_local": recv_local, "ws": ws}
         if ebounds is not None:
@@ -148,9 +178,11 @@ class ShardedTable:
     def update(self, ctx, d_out, lr, deterministic=False, adam_state=None, owner_ws=None):
         ids, ws = ctx["ids"], ctx["ws"]
         if not deterministic:
-            merged = self.ops.merge_by_plan(ids, d_out, self.plan_h, ws)[: ctx["u"]]
+            with self._phase("local MergeAdd"):
+                merged = self.ops.merge_by_plan(ids, d_out, self.plan_h, ws)[: ctx["u"]]
             grads = torch.empty((sum(ctx["recv"]), self.d), dtype=self.dtype, device=d_out.device)
-            all_to_all_rows(grads, merged, ctx["recv"], ctx["send"], self.group)
+            with self._phase("grad all-to-all"):
+                all_to_all_rows(grads, merged, ctx["recv"], ctx["send"], self.group)
             rows = ctx["recv_local"]
             self.bytes_sent += (ctx["u"] - ctx["send"][self.rank]) * self.d * merged.element_size()
         else:
@@ -167,12 +199,13 @@ class ShardedTable:
             all_to_all_rows(grads, sorted_grads[:nvalid], erecv, esend, self.group)
         if rows.numel() == 0:
             return
-        if self.optimizer == "adam":
-            b1p, b2p, beta1, beta2, eps = adam_state
-            self.ops.adam(self.shard, self.m1, self.m2, rows, grads, lr, b1p, b2p, beta1, beta2, eps,
-                          deterministic, owner_ws)
-        else:
-            self.ops.sgd(self.shard, rows, grads, lr, deterministic, owner_ws)
+        with self._phase("owner fused update"):
+            if self.optimizer == "adam":
+                b1p, b2p, beta1, beta2, eps = adam_state
+                self.ops.adam(self.shard, self.m1, self.m2, rows, grads, lr, b1p, b2p, beta1, beta2, eps,
+                              deterministic, owner_ws)
+            else:
+                self.ops.sgd(self.shard, rows, grads, lr, deterministic, owner_ws)
 
     def gather_full_table(self):
         """Debug/parity helper: the full [height, d] table on every rank (interleaved shards)."""
