@@ -1,0 +1,118 @@
+// sum_op.cu — replaces paddle/fluid/operators/sum_op.cu of the reference (op `sum`, X[] -> Out).
+// SelectedRows output: concatenation of the non-empty inputs (sum_op.h:71-145 / SelectedRowsAddTo).
+// LoDTensor output: dense inputs are added element-wise, SelectedRows inputs are accumulated with
+// the duplicate-merging kernel (sum_op.h:40-70 / SelectedRowsAddToTensor).
+#include <memory>
+#include <vector>
+#include "b200_op_common.h"
+#include "paddle/fluid/framework/lod_tensor.h"
+
+namespace paddle {
+namespace operators {
+
+namespace {
+template <typename T>
+__global__ void AddInto(const T* x, int64_t n, T* out) {
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x)
+    out[i] = out[i] + x[i];
+}
+}  // namespace
+
+template <typename T>
+class SumB200Kernel : public framework::OpKernel<T> {
+ public:
+  void Compute(const framework::ExecutionContext& context) const override {
+    using framework::LoDTensor;
+    using framework::SelectedRows;
+    auto in_vars = context.MultiInputVar("X");
+    const int N = static_cast<int>(in_vars.size());
+    auto* out_var = context.OutputVar("Out");
+    const bool in_place = out_var == in_vars[0];
+    auto stream = context.cuda_device_context().stream();
+    const auto place = context.GetPlace();
+
+    if (out_var->IsType<LoDTensor>()) {
+      auto* out = context.Output<LoDTensor>("Out");
+      T* out_data = in_place ? out->data<T>() : out->mutable_data<T>(place);
+      const int64_t numel = out->numel();
+      if (!in_place) PADDLE_ENFORCE(cudaMemsetAsync(out_data, 0, sizeof(T) * numel, stream) == cudaSuccess);
+      for (int i = in_place ? 1 : 0; i < N; ++i) {
+        if (in_vars[i]->IsType<LoDTensor>()) {
+          auto& in_t = in_vars[i]->Get<LoDTensor>();
+          if (in_t.numel() == 0) continue;
+          const int grid = static_cast<int>(std::min<int64_t>((numel + 255) / 256, 148 * 8));
+          AddInto<T><<<grid, 256, 0, stream>>>(in_t.data<T>(), numel, out_data);
+        } else if (in_vars[i]->IsType<SelectedRows>()) {
+          auto& in_t = in_vars[i]->Get<SelectedRows>();
+          const int64_t n = static_cast<int64_t>(in_t.rows().size());
+          if (n == 0) continue;
+          const int64_t height = in_t.height(), d = in_t.value().numel() / n;
+          PADDLE_ENFORCE_EQ(height, out->dims()[0]);
+          framework::Tensor ws;
+          size_t ws_bytes = 0;
+          void* wsp = b200::Workspace(&ws, n, d, sizeof(T), place, &ws_bytes);
+          B200EMB_CHECK(b200::Api<T>::add_to_tensor(in_t.rows().CUDAData(place), in_t.value().data<T>(), n, d, height,
+                                                    out_data, wsp, ws_bytes, b200::Flags(), nullptr, stream));
+        } else {
+          PADDLE_THROW("Variable type must be LoDTensor/SelectedRows.");
+        }
+      }
+    } else if (out_var->IsType<SelectedRows>()) {
+      // an in-place output would be overwritten while it is still an input: snapshot input 0 first
+      std::unique_ptr<SelectedRows> in0;
+      if (in_place) {
+        auto& src = in_vars[0]->Get<SelectedRows>();
+        const int64_t n0 = static_cast<int64_t>(src.rows().size());
+        in0.reset(new SelectedRows(std::vector<int64_t>(), src.height()));
+        in0->mutable_rows()->resize(static_cast<size_t>(n0));
+        in0->mutable_value()->Resize(src.value().dims());
+        if (n0 > 0) {
+          T* v = in0->mutable_value()->mutable_data<T>(place);
+          int64_t* r = in0->mutable_rows()->CUDAMutableData(place);
+          B200EMB_CHECK(b200emb_selected_rows_add_to(src.rows().CUDAData(place), src.value().data<T>(), n0,
+                                                     src.value().numel() / n0, sizeof(T), r, v, 0, stream));
+        }
+      }
+      auto get = [&](int i) -> const SelectedRows& {
+        return (i == 0 && in0) ? *in0 : in_vars[i]->Get<SelectedRows>();
+      };
+      auto* out = context.Output<SelectedRows>("Out");
+      int64_t total = 0;
+      std::vector<int64_t> in_dim;
+      for (int i = 0; i < N; ++i) {
+        const SelectedRows& s = get(i);
+        total += static_cast<int64_t>(s.rows().size());
+        if (in_dim.empty() && s.rows().size() > 0) in_dim = framework::vectorize(s.value().dims());
+      }
+      if (in_dim.empty()) in_dim = framework::vectorize(get(N - 1).value().dims());   // all inputs empty
+      else in_dim[0] = total;
+      out->mutable_rows()->clear();
+      out->mutable_rows()->resize(static_cast<size_t>(total));
+      auto* out_value = out->mutable_value();
+      out_value->Resize(framework::make_ddim(in_dim));
+      T* out_data = out_value->mutable_data<T>(place);
+      if (total == 0) return;
+      int64_t* out_rows = out->mutable_rows()->CUDAMutableData(place);
+      const int64_t d = out_value->numel() / total;
+      int64_t offset = 0;
+      for (int i = 0; i < N; ++i) {
+        const SelectedRows& s = get(i);
+        const int64_t n = static_cast<int64_t>(s.rows().size());
+        if (n == 0) continue;
+        PADDLE_ENFORCE_EQ(out->height(), s.height());
+        B200EMB_CHECK(b200emb_selected_rows_add_to(s.rows().CUDAData(place), s.value().data<T>(), n, d, sizeof(T),
+                                                   out_rows, out_data, offset, stream));
+        offset += n;
+      }
+    } else {
+      PADDLE_THROW("Unexpected branch, output variable type is %s", out_var->Type().name());
+    }
+  }
+};
+
+}  // namespace operators
+}  // namespace paddle
+
+namespace ops = paddle::operators;
+REGISTER_OP_CUDA_KERNEL(sum, ops::SumB200Kernel<float>, ops::SumB200Kernel<double>);
