@@ -316,7 +316,7 @@ k_radix_pass(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ 
 constexpr int kDirectMaxTiles = 64;
 
 template <int BITS>
-__global__ void __launch_bounds__(kSortThreads)
+__global__ void __launch_bounds__(kSortThreads, 4)
 k_prepare_direct(const int64_t* __restrict__ rows, int n, uint32_t height, KeyMap km, int passes,
                  uint32_t* __restrict__ keys, uint32_t* __restrict__ hmat, int32_t* status) {
   constexpr int kBins = 1 << BITS;
@@ -352,7 +352,7 @@ k_prepare_direct(const int64_t* __restrict__ rows, int n, uint32_t height, KeyMa
 }
 
 template <int BITS, bool HAS_PERM_IN>
-__global__ void __launch_bounds__(kSortThreads)
+__global__ void __launch_bounds__(kSortThreads, 4)   // <= 64 registers: fits beside the row kernels on an SM
 k_radix_pass_direct(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ perm_in,
                     uint32_t* __restrict__ keys_out, uint32_t* __restrict__ perm_out, int n,
                     int shift, const uint32_t* __restrict__ hmat, uint32_t* __restrict__ hnext) {
