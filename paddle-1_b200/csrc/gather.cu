@@ -13,7 +13,10 @@
 namespace b200emb {
 namespace {
 
-constexpr int kRowsInFlight = 4;
+#ifndef B200EMB_GATHER_ROWS
+#define B200EMB_GATHER_ROWS 4
+#endif
+constexpr int kRowsInFlight = B200EMB_GATHER_ROWS;
 
 template <typename T, int LPR, int NV, bool VEC>
 __global__ void __launch_bounds__(kBlock, 4)
