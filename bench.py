@@ -337,8 +337,17 @@ def run_single(args):
     else:
         dom = {"kernel": "k_chunk_reduce+k_fixup (fused MergeAdd+SGD)", "bytes": bytes_["upd"], "t": t_update}
     achieved = dom["bytes"] / dom["t"] / 1e9
+    # DRAM traffic of the same kernel(s) from the committed `ncu --set full` capture (profiles/), per launch
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_ncu_full_summary.json")) as f:
+            prof = json.load(f)
+        keys = ["k_gather"] if dom["kernel"].startswith("k_gather") else ["k_chunk_reduce", "k_fixup"]
+        traffic = sum(v["dram_traffic_bytes_per_launch"] for k, v in prof.items() if any(k.startswith(q) for q in keys))
+    except Exception:
+        traffic = None
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "kernel": dom["kernel"], "algorithmic_bytes_per_launch": dom["bytes"],
+                "traffic": traffic, "kernel": dom["kernel"], "algorithmic_bytes_per_launch": dom["bytes"],
                 "peak_source": peak_src,
                 "step": {"algorithmic_bytes": bytes_["step"], "achieved": bytes_["step"] / (ms_per_step * 1e-3) / 1e9,
                          "frac": bytes_["step"] / (ms_per_step * 1e-3) / 1e9 / peak}}
