@@ -47,6 +47,9 @@ extern "C" {
 
 #define B200EMB_DETERMINISTIC 1u
 #define B200EMB_PLAN_READY 2u
+#define B200EMB_UNIQUE_READY 4u   /* with PLAN_READY: the workspace also holds the unique index of
+                                     b200emb_plan_unique_rows for these rows: skip the head scan
+                                     (out_rows / n_unique of merge_add are then not written) */
 
 #define B200EMB_STATUS_BAD_LOOKUP_ID 1
 #define B200EMB_STATUS_BAD_GRAD_ROW 2
@@ -124,6 +127,41 @@ int b200emb_gather_sorted_f32(const float* value, int64_t n, int64_t d, int64_t 
 int b200emb_gather_sorted_f64(const double* value, int64_t n, int64_t d, int64_t plan_height,
                               void* workspace, size_t workspace_bytes, double* out, void* stream);
 
+/* Fused compute + exchange for the row-sharded path (no counterpart in the reference, whose
+ * multi-device SelectedRows path copies whole blocks with cudaMemcpyPeer: memory/memcpy.cc:65-72).
+ * The destinations are device pointers that may live on OTHER GPUs of the box (peer-mapped, e.g.
+ * cudaIpcOpenMemHandle): the kernels store over NVLink while they compute, so no staging buffer and no
+ * separate all-to-all are needed; the caller provides the cross-GPU barrier afterwards.
+ *   lookup_table_scatter: row k of segment g (seg_start[g] <= k < seg_start[g+1], `segs` segments, device
+ *     arrays) of the gathered rows is stored at seg_dst[g] + (k - seg_start[g]) * d  — the owner side of the
+ *     lookup: gather from the shard straight into each requester's buffer.
+ *   merge_add_scatter: merged row u is stored at shard_dst[g] + (u - shard_bounds[g]) * d for the shard g
+ *     with shard_bounds[g] <= u < shard_bounds[g+1]  — the requester side of the update: the local
+ *     duplicate reduction writes straight into each owner's receive buffer.  Needs the plan of
+ *     b200emb_plan_unique_rows in `workspace` (B200EMB_PLAN_READY) or sorts raw rows otherwise.
+ * Destinations must be 16-byte aligned when d*4 is a multiple of 16. */
+int b200emb_lookup_table_scatter_f32(const float* table, int64_t height, int64_t d, const int64_t* ids,
+                                     int64_t n, int64_t padding_idx, const int64_t* seg_start,
+                                     float* const* seg_dst, int64_t segs, int32_t* status, void* stream);
+int b200emb_merge_add_scatter_f32(const int64_t* rows, const float* value, int64_t n, int64_t d,
+                                  int64_t height, const int64_t* shard_bounds, float* const* shard_dst,
+                                  int64_t shards, int64_t* n_unique, void* workspace,
+                                  size_t workspace_bytes, unsigned flags, int32_t* status, void* stream);
+/*   segment_scatter_i64: dst[g][u - bounds[g]] = src[u] for bounds[g] <= u < bounds[g+1] (bounds[segs] =
+ *     element count, read on the device; n_upper = host-side upper bound used to size the grid) — the id
+ *     exchange of the lookup: every rank's unique local rows go straight into their owners' buffers. */
+int b200emb_segment_scatter_i64(const int64_t* src, int64_t n_upper, const int64_t* bounds,
+                                int64_t* const* dst, int64_t segs, void* stream);
+
+/* Set-up utilities for the peer-store kernels above (NOT on the step path; the only entry points that
+ * allocate): a device buffer exported through CUDA IPC so that the other ranks' GPUs can store into it,
+ * and the import side (cudaIpcOpenMemHandle with lazy peer access).  `handle64` is the 64-byte
+ * cudaIpcMemHandle_t, exchanged by the caller (e.g. torch.distributed.all_gather_object). */
+int b200emb_peer_alloc(size_t bytes, void** ptr, unsigned char* handle64);
+int b200emb_peer_open(const unsigned char* handle64, void** ptr);
+int b200emb_peer_close(void* ptr);
+int b200emb_peer_free(void* ptr);
+
 /* scatter::MergeAdd — replaces math/selected_rows_functor.cu:235-297 (CPU semantics
  * selected_rows_functor.cc:193-228): out_rows = ascending unique rows, out_value[u,:] = sum of
  * the input rows with that id.  out_rows/out_value must hold n rows; *n_unique (device int64)
@@ -178,6 +216,18 @@ int b200emb_sparse_adam_f64(double* param, double* moment1, double* moment2, int
                             float beta1, float beta2, float epsilon, void* workspace,
                             size_t workspace_bytes, unsigned flags, int32_t* status,
                             void* stream);
+
+/* sparse Adagrad, in place — replaces SparseAdagradFunctor (operators/adagrad_op.cu:26-108;
+ * CPU semantics adagrad_op.cc:108-141): merged = MergeAdd(grad); moment[r] += merged^2;
+ * param[r] -= lr * merged / (sqrt(moment[r]) + epsilon), fused in one pass like sgd/adam. */
+int b200emb_sparse_adagrad_f32(float* param, float* moment, int64_t height, int64_t d,
+                               const int64_t* rows, const float* grad, int64_t n, const float* lr,
+                               float epsilon, void* workspace, size_t workspace_bytes, unsigned flags,
+                               int32_t* status, void* stream);
+int b200emb_sparse_adagrad_f64(double* param, double* moment, int64_t height, int64_t d,
+                               const int64_t* rows, const double* grad, int64_t n, const double* lr,
+                               float epsilon, void* workspace, size_t workspace_bytes, unsigned flags,
+                               int32_t* status, void* stream);
 
 /* Sparse SGD without a workspace argument — NO COUNTERPART IN THE REFERENCE (its kernels take
  * temporaries from Fluid's allocator).  Same result as b200emb_sparse_sgd_f32; the scratch is a

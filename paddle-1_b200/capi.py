@@ -13,6 +13,7 @@ _LIB_PATH = os.path.join(_HERE, "libb200emb.so")
 
 DETERMINISTIC = 1
 PLAN_READY = 2
+UNIQUE_READY = 4
 
 _ERRORS = {-1: "invalid argument", -2: "workspace missing/misaligned/too small",
            -3: "CUDA error", -4: "size beyond supported limits",
@@ -28,9 +29,11 @@ EXPORTS = [
     "b200emb_selected_rows_add_to_tensor_f32", "b200emb_selected_rows_add_to_tensor_f64",
     "b200emb_sparse_sgd_f32", "b200emb_sparse_sgd_f64",
     "b200emb_sparse_adam_f32", "b200emb_sparse_adam_f64",
-    "b200emb_sparse_sgd_noalloc_f32",
+    "b200emb_sparse_sgd_noalloc_f32", "b200emb_sparse_adagrad_f32", "b200emb_sparse_adagrad_f64",
     "b200emb_plan_unique_rows", "b200emb_expand_unique_f32", "b200emb_expand_unique_f64",
     "b200emb_gather_sorted_f32", "b200emb_gather_sorted_f64",
+    "b200emb_lookup_table_scatter_f32", "b200emb_merge_add_scatter_f32", "b200emb_segment_scatter_i64",
+    "b200emb_peer_alloc", "b200emb_peer_open", "b200emb_peer_close", "b200emb_peer_free",
 ]
 
 _lib = None
@@ -86,11 +89,11 @@ def _need_cuda(*tensors):
 
 
 def radix_passes(n, height):
-    """Radix passes of the sort plan (sort.cu digit_plan): <=10-bit digits up to 64 tiles of 2048, else 8-bit."""
+    """Radix passes of the sort plan (sort.cu digit_plan): <=10-bit digits up to 64 tiles of 2048, else <=9-bit."""
     bits = 1
     while (1 << bits) <= int(height):
         bits += 1
-    maxb = 10 if (n + 2047) // 2048 <= 64 else 8
+    maxb = 10 if (n + 2047) // 2048 <= 64 else 9
     return (bits + maxb - 1) // maxb
 
 
@@ -303,3 +306,88 @@ def gather_sorted(value, plan_h, workspace, out=None):
     if out is None:
         out = torch.empty_like(value)
     return _permute("b200emb_gather_sorted_", value, n, d, plan_h, workspace, out)
+
+
+# ---------------------------------------------------------------- peer-store (fused exchange) helpers
+class PeerBuffer:
+    """A device buffer that other ranks' GPUs can store into (CUDA IPC).  Set-up only."""
+
+    def __init__(self, nbytes):
+        self.nbytes = int(nbytes)
+        ptr = ctypes.c_void_p()
+        handle = (ctypes.c_ubyte * 64)()
+        _check(lib().b200emb_peer_alloc(ctypes.c_size_t(self.nbytes), ctypes.byref(ptr), handle), "peer_alloc")
+        self.ptr = int(ptr.value)
+        self.handle = bytes(handle)
+        self.opened = {}
+
+    def tensor(self, shape, dtype):
+        """torch view of the first prod(shape) elements (no ownership)."""
+        n = 1
+        for x in shape:
+            n *= int(x)
+        item = torch.empty(0, dtype=dtype).element_size()
+        assert n * item <= self.nbytes
+        typestr = {torch.float32: "<f4", torch.float64: "<f8", torch.int64: "<i8", torch.uint8: "|u1"}[dtype]
+
+        class _Iface:
+            pass
+        o = _Iface()
+        o.__cuda_array_interface__ = {"shape": tuple(int(x) for x in shape), "typestr": typestr,
+                                      "data": (self.ptr, False), "version": 2}
+        return torch.as_tensor(o, device="cuda")
+
+    def free(self):
+        if self.ptr:
+            lib().b200emb_peer_free(ctypes.c_void_p(self.ptr))
+            self.ptr = 0
+
+
+def peer_open(handle_bytes):
+    ptr = ctypes.c_void_p()
+    buf = (ctypes.c_ubyte * 64).from_buffer_copy(handle_bytes)
+    _check(lib().b200emb_peer_open(buf, ctypes.byref(ptr)), "peer_open")
+    return int(ptr.value)
+
+
+def lookup_table_scatter(table, ids, seg_start, seg_dst, status=None, padding_idx=-1):
+    """Gather rows table[ids[k]] and store row k of segment g at seg_dst[g] + (k - seg_start[g]) * d.
+    seg_start: int64 device tensor [G+1]; seg_dst: int64 device tensor [G] of (possibly peer) addresses."""
+    _need_cuda(table, ids, seg_start, seg_dst, status)
+    v, d = table.shape
+    _check(lib().b200emb_lookup_table_scatter_f32(
+        _ptr(table), ctypes.c_int64(v), ctypes.c_int64(d), _ptr(ids), ctypes.c_int64(ids.numel()),
+        ctypes.c_int64(padding_idx), _ptr(seg_start), _ptr(seg_dst), ctypes.c_int64(seg_dst.numel()),
+        _ptr(status), _stream()), "lookup_table_scatter")
+
+
+def merge_add_scatter(rows, value, height, shard_bounds, shard_dst, workspace, flags=0, status=None):
+    """MergeAdd whose merged row u is stored at shard_dst[g] + (u - shard_bounds[g]) * d (peer stores)."""
+    _need_cuda(rows, value, shard_bounds, shard_dst, workspace, status)
+    n, d = value.shape
+    _check(lib().b200emb_merge_add_scatter_f32(
+        _ptr(rows), _ptr(value), ctypes.c_int64(n), ctypes.c_int64(d), ctypes.c_int64(height),
+        _ptr(shard_bounds), _ptr(shard_dst), ctypes.c_int64(shard_dst.numel()), None, _ptr(workspace),
+        ctypes.c_size_t(workspace.numel()), ctypes.c_uint(flags), _ptr(status), _stream()), "merge_add_scatter")
+
+
+def segment_scatter_i64(src, n_upper, bounds, dst):
+    """dst[g][u - bounds[g]] = src[u] for every u < bounds[-1] (destinations may be peer GPUs)."""
+    _need_cuda(src, bounds, dst)
+    _check(lib().b200emb_segment_scatter_i64(_ptr(src), ctypes.c_int64(n_upper), _ptr(bounds), _ptr(dst),
+                                             ctypes.c_int64(dst.numel()), _stream()), "segment_scatter_i64")
+
+
+def sparse_adagrad(param, moment, rows, grad, lr, epsilon=1e-6, workspace=None, flags=0, status=None):
+    """In-place sparse Adagrad = MergeAdd fused with the moment/parameter row update (adagrad_op.cc:108-141)."""
+    _need_cuda(param, moment, rows, grad, lr, workspace, status)
+    n = rows.numel()
+    v, d = param.shape
+    if workspace is None:
+        workspace = alloc_workspace(n, d, param.element_size(), param.device)
+    fn = getattr(lib(), "b200emb_sparse_adagrad_" + _sfx(param.dtype))
+    _check(fn(_ptr(param), _ptr(moment), ctypes.c_int64(v), ctypes.c_int64(d), _ptr(rows), _ptr(grad),
+              ctypes.c_int64(n), _ptr(lr), ctypes.c_float(epsilon), _ptr(workspace),
+              ctypes.c_size_t(workspace.numel()), ctypes.c_uint(flags), _ptr(status), _stream()),
+           "sparse_adagrad")
+    return param

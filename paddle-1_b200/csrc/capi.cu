@@ -60,8 +60,11 @@ int run_update(const int64_t* rows, const T* value, int64_t n, int64_t d, int64_
     if (e != cudaSuccess) return fail_cuda(e);
   }
   if (det || args.op == UpdateOp::kMergeAdd) {
-    e = launch_head_scan(plan, n, static_cast<uint32_t>(height), ws, L, out_rows, n_unique, s);
-    if (e != cudaSuccess) return fail_cuda(e);
+    const bool have_unique = (flags & B200EMB_PLAN_READY) && (flags & B200EMB_UNIQUE_READY);
+    if (!have_unique) {
+      e = launch_head_scan(plan, n, static_cast<uint32_t>(height), ws, L, out_rows, n_unique, s);
+      if (e != cudaSuccess) return fail_cuda(e);
+    }
     args.uidx = reinterpret_cast<const uint32_t*>(ws + L.off_uidx);
   }
   e = launch_update<T>(plan, value, n, d, height, args, det, ws, L, status, s);
@@ -236,6 +239,46 @@ int b200emb_gather_sorted_f64(const double* value, int64_t n, int64_t d, int64_t
   return run_permute<double>(value, n, d, plan_height, workspace, workspace_bytes, out, false, stream);
 }
 
+// ---- peer-store variants for the sharded path (destinations may be other GPUs' memory) ----------
+int b200emb_lookup_table_scatter_f32(const float* table, int64_t height, int64_t d, const int64_t* ids,
+                                     int64_t n, int64_t padding_idx, const int64_t* seg_start,
+                                     float* const* seg_dst, int64_t segs, int32_t* status, void* stream) {
+  int rc = check_sizes(n, d, height);
+  if (rc != B200EMB_OK) return rc;
+  if (n == 0) return B200EMB_OK;
+  if (!table || !ids || !seg_start || !seg_dst || segs < 1 || segs > 4096) return B200EMB_E_INVALID;
+  cudaError_t e = launch_gather<float>(table, height, d, ids, n, padding_idx, nullptr, status,
+                                       static_cast<cudaStream_t>(stream), seg_start, seg_dst,
+                                       static_cast<int>(segs));
+  return e == cudaSuccess ? B200EMB_OK : fail_cuda(e);
+}
+
+int b200emb_segment_scatter_i64(const int64_t* src, int64_t n_upper, const int64_t* bounds,
+                                int64_t* const* dst, int64_t segs, void* stream) {
+  if (n_upper < 0 || segs < 1 || segs > 4096) return B200EMB_E_INVALID;
+  if (n_upper == 0) return B200EMB_OK;
+  if (!src || !bounds || !dst) return B200EMB_E_INVALID;
+  cudaError_t e = launch_segment_scatter_i64(src, n_upper, bounds, dst, static_cast<int>(segs),
+                                             static_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? B200EMB_OK : fail_cuda(e);
+}
+
+int b200emb_merge_add_scatter_f32(const int64_t* rows, const float* value, int64_t n, int64_t d,
+                                  int64_t height, const int64_t* shard_bounds, float* const* shard_dst,
+                                  int64_t shards, int64_t* n_unique, void* workspace,
+                                  size_t workspace_bytes, unsigned flags, int32_t* status, void* stream) {
+  if (shards < 1 || shards > 4096 || !shard_bounds || !shard_dst) return B200EMB_E_INVALID;
+  UpdateArgs<float> a;
+  a.op = UpdateOp::kMergeAdd;
+  a.param = const_cast<float*>(value);   // unused (every row goes through the scatter map); non-null for the checks
+  a.shard_bounds = shard_bounds;
+  a.shard_dst = shard_dst;
+  a.shards = static_cast<int>(shards);
+  a.dst_aligned16 = (d % 4) == 0;        // destinations are required to be 16-byte aligned buffers
+  return run_update<float>(rows, value, n, d, height, a, /*out_rows=*/nullptr, n_unique, workspace,
+                           workspace_bytes, flags, status, stream, true);
+}
+
 #define B200EMB_DEFINE_UPDATES(T, S)                                                             \
   int b200emb_merge_add_##S(const int64_t* rows, const T* value, int64_t n, int64_t d,           \
                             int64_t height, int64_t* out_rows, T* out_value, int64_t* n_unique,  \
@@ -288,6 +331,23 @@ int b200emb_gather_sorted_f64(const double* value, int64_t n, int64_t d, int64_t
                          workspace_bytes, flags, status, stream,                                 \
                          lr && beta1_pow && beta2_pow && moment1 && moment2);                    \
   }
+
+#define B200EMB_DEFINE_ADAGRAD(T, S)                                                             \
+  int b200emb_sparse_adagrad_##S(T* param, T* moment, int64_t height, int64_t d,                 \
+                                 const int64_t* rows, const T* grad, int64_t n, const T* lr,     \
+                                 float epsilon, void* workspace, size_t workspace_bytes,         \
+                                 unsigned flags, int32_t* status, void* stream) {                \
+    UpdateArgs<T> a;                                                                             \
+    a.op = UpdateOp::kAdagrad;                                                                   \
+    a.param = param;                                                                             \
+    a.moment1 = moment;                                                                          \
+    a.lr = lr;                                                                                   \
+    a.epsilon = static_cast<T>(epsilon);                                                         \
+    return run_update<T>(rows, grad, n, d, height, a, nullptr, nullptr, workspace,               \
+                         workspace_bytes, flags, status, stream, lr && moment);                  \
+  }
+B200EMB_DEFINE_ADAGRAD(float, f32)
+B200EMB_DEFINE_ADAGRAD(double, f64)
 
 B200EMB_DEFINE_UPDATES(float, f32)
 B200EMB_DEFINE_UPDATES(double, f64)

@@ -21,7 +21,8 @@ constexpr int kRowsInFlight = B200EMB_GATHER_ROWS;
 template <typename T, int LPR, int NV, bool VEC>
 __global__ void __launch_bounds__(kBlock, 4)
 k_gather(const T* __restrict__ table, const int64_t* __restrict__ ids, T* __restrict__ out,
-         int64_t n, int64_t height, int d, int64_t padding_idx, int32_t* status) {
+         int64_t n, int64_t height, int d, int64_t padding_idx, int32_t* status,
+         const int64_t* __restrict__ seg_start, T* const* __restrict__ seg_dst, int segs) {
   constexpr int EPV = Epv<T, VEC>::value;
   constexpr int kGroups = kBlock / LPR;
   const int l = threadIdx.x % LPR;
@@ -72,8 +73,16 @@ k_gather(const T* __restrict__ table, const int64_t* __restrict__ ids, T* __rest
 #pragma unroll
         for (int kk = 0; kk < NV; ++kk) {
           const int col = col0 + (l + kk * LPR) * EPV;
-          if (live[r] && col < d)
-            store_vec_stream<T, VEC>(out + (base + r * num_groups) * d + col, v[r][kk]);
+          if (live[r] && col < d) {
+            const int64_t k = base + r * num_groups;
+            T* dst = out + k * d;
+            if (segs > 0) {   // scatter to per-segment destinations (peer GPUs in the sharded path)
+              int g = 0;
+              while (g + 1 < segs && k >= seg_start[g + 1]) ++g;
+              dst = seg_dst[g] + (k - seg_start[g]) * d;
+            }
+            store_vec_stream<T, VEC>(dst + col, v[r][kk]);
+          }
         }
     }
   }
@@ -84,9 +93,10 @@ k_gather(const T* __restrict__ table, const int64_t* __restrict__ ids, T* __rest
 
 template <typename T>
 cudaError_t launch_gather(const T* table, int64_t height, int64_t d, const int64_t* ids, int64_t n,
-                          int64_t padding_idx, T* out, int32_t* status, cudaStream_t s) {
+                          int64_t padding_idx, T* out, int32_t* status, cudaStream_t s,
+                          const int64_t* seg_start, T* const* seg_dst, int segs) {
   if (n == 0) return cudaSuccess;
-  const bool aligned = is_aligned16(table) && is_aligned16(out);
+  const bool aligned = is_aligned16(table) && (segs > 0 || is_aligned16(out));
   cudaError_t err = cudaSuccess;
   dispatch_row_shape<T>(d, aligned, [&]<int LPR, int NV, bool VEC>() {
     constexpr int kGroups = kBlock / LPR;
@@ -94,15 +104,18 @@ cudaError_t launch_gather(const T* table, int64_t height, int64_t d, const int64
     const int64_t want = ceil_div(n, static_cast<int64_t>(kGroups));
     const int grid = static_cast<int>(std::min<int64_t>(want, 148 * 4));
     k_gather<T, LPR, NV, VEC><<<grid, kBlock, 0, s>>>(table, ids, out, n, height,
-                                                      static_cast<int>(d), padding_idx, status);
+                                                      static_cast<int>(d), padding_idx, status,
+                                                      seg_start, seg_dst, segs);
     err = cudaGetLastError();
   });
   return err;
 }
 
 template cudaError_t launch_gather<float>(const float*, int64_t, int64_t, const int64_t*, int64_t,
-                                          int64_t, float*, int32_t*, cudaStream_t);
+                                          int64_t, float*, int32_t*, cudaStream_t, const int64_t*,
+                                          float* const*, int);
 template cudaError_t launch_gather<double>(const double*, int64_t, int64_t, const int64_t*, int64_t,
-                                           int64_t, double*, int32_t*, cudaStream_t);
+                                           int64_t, double*, int32_t*, cudaStream_t, const int64_t*,
+                                           double* const*, int);
 
 }  // namespace b200emb

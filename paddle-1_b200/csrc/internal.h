@@ -90,12 +90,15 @@ cudaError_t launch_cluster_sort(const int64_t* rows, int64_t n, int64_t height, 
                                 cudaStream_t s);
 
 // gather.cu
+// `seg_start`/`seg_dst` (device arrays, `segs` entries + 1 / `segs` entries) optionally scatter the output:
+// row k of segment g (seg_start[g] <= k < seg_start[g+1]) is stored at seg_dst[g] + (k - seg_start[g]) * d.
 template <typename T>
 cudaError_t launch_gather(const T* table, int64_t height, int64_t d, const int64_t* ids, int64_t n,
-                          int64_t padding_idx, T* out, int32_t* status, cudaStream_t s);
+                          int64_t padding_idx, T* out, int32_t* status, cudaStream_t s,
+                          const int64_t* seg_start = nullptr, T* const* seg_dst = nullptr, int segs = 0);
 
 // segreduce.cu
-enum class UpdateOp { kMergeAdd, kAddToTensor, kSgd, kAdam };
+enum class UpdateOp { kMergeAdd, kAddToTensor, kSgd, kAdam, kAdagrad };
 template <typename T>
 struct UpdateArgs {
   UpdateOp op;
@@ -107,6 +110,10 @@ struct UpdateArgs {
   const T* beta2_pow = nullptr;
   T beta1 = 0, beta2 = 0, epsilon = 0;
   const uint32_t* uidx = nullptr;  // kMergeAdd: sorted position -> output row
+  const int64_t* shard_bounds = nullptr;   // kMergeAdd scatter map (device arrays), see segreduce.cu Params
+  T* const* shard_dst = nullptr;
+  int shards = 0;
+  bool dst_aligned16 = true;               // caller's promise about the scatter destinations
 };
 template <typename T>
 cudaError_t launch_update(const SortedPlan& plan, const T* value, int64_t n, int64_t d,
@@ -120,6 +127,8 @@ cudaError_t launch_shard_split(const int64_t* ukeys, const SortedPlan& plan, cha
                                const Workspace& L, int shards, uint32_t shard_height, int64_t n,
                                uint32_t invalid_key, int64_t* bounds, int64_t* elem_bounds,
                                int64_t* local_rows, cudaStream_t s);
+cudaError_t launch_segment_scatter_i64(const int64_t* src, int64_t n_upper, const int64_t* bounds,
+                                       int64_t* const* dst, int segs, cudaStream_t s);
 template <typename T>
 cudaError_t launch_permute_rows(const T* src, const SortedPlan& plan, const uint32_t* uidx, int64_t n,
                                 int64_t d, T* out, bool unique, cudaStream_t s);

@@ -6,6 +6,7 @@
 //   kAddToTensor  tensor[id,:]   += sum           SelectedRowsAddToTensor (:153-178)
 //   kSgd          param[id,:]    -= lr*sum        sparse SGD (sgd_op.h:47-81)
 //   kAdam         lazy Adam on (param,m1,m2)[id]  SparseAdamFunctor (adam_op.h:199-219)
+//   kAdagrad      moment += sum^2; param -= lr*sum/(sqrt(moment)+eps)   SparseAdagradFunctor (adagrad_op.cc:108-141)
 // so merged gradient rows never travel through HBM: each input row is read once, each touched
 // parameter row is read and written once.
 //
@@ -42,6 +43,12 @@ struct Params {
   const uint32_t* uidx;
   int d;
   uint32_t height;
+  // kMergeAdd with a scatter map: merged row u goes to shard_dst[g] + (u - shard_bounds[g]) * d for the
+  // shard g with shard_bounds[g] <= u < shard_bounds[g+1].  The destinations may be peer-GPU memory
+  // (NVLink stores), which fuses the local pre-reduction with the gradient all-to-all.
+  const int64_t* shard_bounds;
+  T* const* shard_dst;
+  int shards;
 };
 
 template <typename T>
@@ -62,7 +69,8 @@ __device__ __forceinline__ void zero_acc(T (&a)[NV][EPV]) {
 // loads (parameter / moment rows) of several rows together with the gradient-row loads and pay
 // one memory round trip per batch instead of one per row.
 template <UpdateOp OP> struct NumState {
-  static constexpr int value = OP == UpdateOp::kAdam ? 3 : (OP == UpdateOp::kMergeAdd ? 0 : 1);
+  static constexpr int value =
+      OP == UpdateOp::kAdam ? 3 : (OP == UpdateOp::kAdagrad ? 2 : (OP == UpdateOp::kMergeAdd ? 0 : 1));
 };
 template <typename T, UpdateOp OP, int NV, int EPV>
 struct RowState { T v[NumState<OP>::value == 0 ? 1 : NumState<OP>::value][NV][EPV]; };
@@ -83,6 +91,7 @@ __device__ __forceinline__ void load_state(const Params<T>& P, uint32_t key, int
       load_vec<T, VEC>(P.m1 + base + col, st.v[1][k]);
       load_vec<T, VEC>(P.m2 + base + col, st.v[2][k]);
     }
+    if constexpr (OP == UpdateOp::kAdagrad) load_vec<T, VEC>(P.m1 + base + col, st.v[1][k]);
   }
 }
 
@@ -97,12 +106,20 @@ __device__ __forceinline__ void apply_state(const Params<T>& P, uint32_t key, ui
   const int64_t row = (OP == UpdateOp::kMergeAdd) ? static_cast<int64_t>(P.uidx[eref])
                                                   : static_cast<int64_t>(key);
   const int64_t base = row * P.d;
+  T* merge_dst = P.param + base;
+  if constexpr (OP == UpdateOp::kMergeAdd) {
+    if (P.shards > 0) {
+      int g = 0;
+      while (g + 1 < P.shards && row >= P.shard_bounds[g + 1]) ++g;
+      merge_dst = P.shard_dst[g] + (row - P.shard_bounds[g]) * P.d;
+    }
+  }
 #pragma unroll
   for (int k = 0; k < NV; ++k) {
     const int col = col0 + (l + k * LPR) * EPV;
     if (col >= P.d) continue;
     if constexpr (OP == UpdateOp::kMergeAdd) {
-      store_vec<T, VEC>(P.param + base + col, acc[k]);
+      store_vec<T, VEC>(merge_dst + col, acc[k]);
     } else if constexpr (OP == UpdateOp::kAddToTensor) {
 #pragma unroll
       for (int e = 0; e < EPV; ++e) st.v[0][k][e] = A::add(st.v[0][k][e], acc[k][e]);
@@ -111,6 +128,19 @@ __device__ __forceinline__ void apply_state(const Params<T>& P, uint32_t key, ui
       const T lr = *P.lr;
 #pragma unroll
       for (int e = 0; e < EPV; ++e) st.v[0][k][e] = A::sub(st.v[0][k][e], A::mul(lr, acc[k][e]));
+      store_vec<T, VEC>(P.param + base + col, st.v[0][k]);
+    } else if constexpr (OP == UpdateOp::kAdagrad) {
+      // adagrad_op.cc:119-138: moment += g*g (scatter::Mul + SelectedRowsAddToTensor), then
+      // param -= lr*g / (sqrt(moment) + eps), evaluated left to right
+      const T lr = *P.lr;
+#pragma unroll
+      for (int e = 0; e < EPV; ++e) {
+        const T g = acc[k][e];
+        const T m = A::add(st.v[1][k][e], A::mul(g, g));
+        st.v[1][k][e] = m;
+        st.v[0][k][e] = A::sub(st.v[0][k][e], A::div(A::mul(lr, g), A::add(A::sqrt(m), P.eps)));
+      }
+      store_vec<T, VEC>(P.m1 + base + col, st.v[1][k]);
       store_vec<T, VEC>(P.param + base + col, st.v[0][k]);
     } else {  // kAdam — operation order of adam_op.h:209-213, every step rounded in T
       const T one = T(1);
@@ -530,13 +560,14 @@ cudaError_t launch_op(const SortedPlan& plan, const T* value, int64_t n, int64_t
                       cudaStream_t s) {
   Params<T> P{a.param, a.moment1, a.moment2, a.lr, a.beta1_pow, a.beta2_pow,
               a.beta1, a.beta2, a.epsilon, a.uidx, static_cast<int>(d),
-              static_cast<uint32_t>(height)};
+              static_cast<uint32_t>(height), a.shard_bounds, a.shard_dst, a.shards};
   Carry<T> C{reinterpret_cast<uint32_t*>(ws + L.off_cta_flags),
              reinterpret_cast<uint32_t*>(ws + L.off_cta_tail_key),
              reinterpret_cast<uint32_t*>(ws + L.off_cta_tail_eref),
              reinterpret_cast<T*>(ws + L.off_cta_head), reinterpret_cast<T*>(ws + L.off_cta_tail)};
-  bool aligned = is_aligned16(value) && is_aligned16(a.param);
+  bool aligned = is_aligned16(value) && (a.shards > 0 || is_aligned16(a.param)) && a.dst_aligned16;
   if (OP == UpdateOp::kAdam) aligned = aligned && is_aligned16(a.moment1) && is_aligned16(a.moment2);
+  if (OP == UpdateOp::kAdagrad) aligned = aligned && is_aligned16(a.moment1);
   cudaError_t err = cudaSuccess;
   const int ni = static_cast<int>(n);
   dispatch_row_shape<T>(d, aligned, [&]<int LPR, int NV, bool VEC>() {
@@ -598,6 +629,8 @@ cudaError_t launch_update(const SortedPlan& plan, const T* value, int64_t n, int
       return launch_op<T, UpdateOp::kSgd>(plan, value, n, d, height, a, deterministic, ws, L, s);
     case UpdateOp::kAdam:
       return launch_op<T, UpdateOp::kAdam>(plan, value, n, d, height, a, deterministic, ws, L, s);
+    case UpdateOp::kAdagrad:
+      return launch_op<T, UpdateOp::kAdagrad>(plan, value, n, d, height, a, deterministic, ws, L, s);
   }
   return cudaErrorInvalidValue;
 }

@@ -56,6 +56,19 @@ k_shard_split(const int64_t* __restrict__ ukeys, const PlanHeader* hdr, int shar
       local_rows[u] = ukeys[u] % shard_height;
 }
 
+// dst[g][u - bounds[g]] = src[u] for bounds[g] <= u < bounds[g+1]; dst may be peer-GPU memory
+__global__ void __launch_bounds__(256)
+k_segment_scatter_i64(const int64_t* __restrict__ src, const int64_t* __restrict__ bounds,
+                      int64_t* const* __restrict__ dst, int segs) {
+  const int64_t total = bounds[segs];
+  for (int64_t u = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; u < total;
+       u += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    int g = 0;
+    while (g + 1 < segs && u >= bounds[g + 1]) ++g;
+    dst[g][u - bounds[g]] = src[u];
+  }
+}
+
 // out[perm[e], :] = src[uidx[e], :]  (UNIQUE)   or   out[e, :] = src[perm[e], :]  (!UNIQUE)
 template <typename T, int LPR, int NV, bool VEC, bool UNIQUE>
 __global__ void __launch_bounds__(kBlock, 4)
@@ -114,6 +127,13 @@ cudaError_t launch_shard_split(const int64_t* ukeys, const SortedPlan& plan, cha
                                      shard_height, reinterpret_cast<const uint32_t*>(ws + L.off_seg_start),
                                      plan.keys, static_cast<int>(n), invalid_key, bounds, elem_bounds,
                                      local_rows);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_segment_scatter_i64(const int64_t* src, int64_t n_upper, const int64_t* bounds,
+                                       int64_t* const* dst, int segs, cudaStream_t s) {
+  const int grid = static_cast<int>(std::min<int64_t>(std::max<int64_t>(ceil_div(n_upper, 256), 1), 148 * 8));
+  k_segment_scatter_i64<<<grid, 256, 0, s>>>(src, bounds, dst, segs);
   return cudaGetLastError();
 }
 

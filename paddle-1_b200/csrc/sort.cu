@@ -555,12 +555,13 @@ int key_bits(int64_t height) {  // keys span [0, height] (height = the invalid s
 // of up to 10 bits to save passes.  Larger batches keep 8-bit digits (the chained scan's walk
 // costs one counter per bin per predecessor tile, so wide digits lose there).
 constexpr int kDirectMaxBits = 10;
+constexpr int kLookbackMaxBits = 9;   // 27-bit keys (100M-row tables) sort in 3 passes instead of 4
 struct DigitPlan { int passes, bits; bool direct; };
 DigitPlan digit_plan(int64_t n, int64_t height) {
   const int kb = key_bits(height);
   DigitPlan p;
   p.direct = ceil_div(n, kSortTile) <= kDirectMaxTiles;
-  const int maxb = p.direct ? kDirectMaxBits : kRadixBits;
+  const int maxb = p.direct ? kDirectMaxBits : kLookbackMaxBits;
   p.passes = static_cast<int>(ceil_div(kb, maxb));
   p.bits = static_cast<int>(ceil_div(kb, p.passes));
   if (p.bits < kRadixBits) p.bits = kRadixBits;
@@ -568,7 +569,7 @@ DigitPlan digit_plan(int64_t n, int64_t height) {
 }
 // counter words per tile the workspace must hold for any height at this n
 int64_t lookback_words_per_tile(int64_t n) {
-  return ceil_div(n, kSortTile) <= kDirectMaxTiles ? 4LL * (1 << kDirectMaxBits) : 4LL * kRadix;
+  return ceil_div(n, kSortTile) <= kDirectMaxTiles ? 4LL * (1 << kDirectMaxBits) : 4LL * (1 << kLookbackMaxBits);
 }
 
 }  // namespace
@@ -718,7 +719,8 @@ cudaError_t launch_plan(const int64_t* rows, int64_t n, int64_t height, char* ws
                                              L.sort_tiles * (1u << dp.bits);
     e = cudaMemsetAsync(ws, 0, std::min(zero, L.zero_bytes), s);
     if (e != cudaSuccess) return e;
-    e = launch_passes<8>(rows, ni, h, km, dp.passes, ws, L, status, s);
+    e = dp.bits == 9 ? launch_passes<9>(rows, ni, h, km, dp.passes, ws, L, status, s)
+                     : launch_passes<8>(rows, ni, h, km, dp.passes, ws, L, status, s);
   }
   if (e != cudaSuccess) return e;
   if (out) *out = plan_view(n, height, ws, L);

@@ -92,7 +92,7 @@ fw::AttributeMap ParseAttrs(const char* spec) {
 // which input decides the kernel's data type (GetExpectedKernelType of each op)
 const char* KeySlot(const std::string& type) {
   if (type == "lookup_table" || type == "lookup_table_grad") return "W";   // lookup_table_op.cc:53-57
-  if (type == "sgd" || type == "adam") return "Param";                     // sgd_op.cc:44-48, adam_op.cc:76-81
+  if (type == "sgd" || type == "adam" || type == "adagrad") return "Param";  // sgd_op.cc:44-48, adam_op.cc:76-81
   return "X";                                                              // sum_op.cc:67-127
 }
 }  // namespace

@@ -25,6 +25,7 @@ OP_SLOTS = {
     "sgd": (["Param", "Grad", "LearningRate"], ["ParamOut"]),
     "adam": (["Param", "Grad", "LearningRate", "Moment1", "Moment2", "Beta1Pow", "Beta2Pow"],
              ["ParamOut", "Moment1Out", "Moment2Out"]),
+    "adagrad": (["Param", "Grad", "Moment", "LearningRate"], ["ParamOut", "MomentOut"]),
 }
 # attributes with their defaults (OpAttrChecker defaults: lookup_table_op.cc:71-83, adam_op.cc:99-112)
 OP_ATTRS = {
@@ -33,6 +34,7 @@ OP_ATTRS = {
     "sum": {},
     "sgd": {},
     "adam": {"beta1": ("f", 0.9), "beta2": ("f", 0.999), "epsilon": ("f", 1.0e-8)},
+    "adagrad": {"epsilon": ("f", 1.0e-6)},
 }
 
 

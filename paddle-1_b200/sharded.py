@@ -54,6 +54,17 @@ class CudaOps:
     def lookup(self, shard, local_rows):
         return self.capi.lookup_table(shard, local_rows)
 
+    # fused compute + exchange: the kernels store straight into peer GPUs' buffers over NVLink
+    def lookup_scatter(self, shard, local_rows, seg_start, seg_dst):
+        self.capi.lookup_table_scatter(shard, local_rows, seg_start, seg_dst)
+
+    def ids_scatter(self, local_rows, n_upper, bounds, dst):
+        self.capi.segment_scatter_i64(local_rows, n_upper, bounds, dst)
+
+    def merge_scatter(self, ids, value, plan_h, shard_bounds, shard_dst, ws):
+        self.capi.merge_add_scatter(ids, value, plan_h, shard_bounds, shard_dst, ws,
+                                    flags=self.capi.PLAN_READY | self.capi.UNIQUE_READY)
+
     def sgd(self, shard, rows, grads, lr, deterministic, ws=None):
         flags = self.capi.DETERMINISTIC if deterministic else 0
         self.capi.sparse_sgd(shard, rows, grads, lr, workspace=ws, flags=flags)
@@ -130,10 +141,48 @@ class ShardedTable:
             self.m1 = torch.zeros_like(self.shard)
             self.m2 = torch.zeros_like(self.shard)
         self.bytes_sent = 0
+        self.peer = False
         self.phase_events = None      # set to [] to record (name, start_event, end_event) per phase
 
     def _phase(self, name):
         return _Phase(self, name)
+
+    def enable_peer_exchange(self, cap_unique, cap_recv):
+        """Set-up (once): exchange CUDA-IPC handles of two receive buffers per rank so that the owner's
+        gather kernel and the requester's MergeAdd kernel can store straight into the other GPUs' memory
+        (fused compute + all-to-all over NVLink).  Steps whose sizes exceed the capacities fall back to NCCL."""
+        if self.world == 1:
+            return False
+        capi = self.ops.capi
+        item = torch.empty(0, dtype=self.dtype).element_size()
+        self.cap_u, self.cap_r = int(cap_unique), int(cap_recv)
+        self.peer_u = capi.PeerBuffer(self.cap_u * self.d * item)
+        self.peer_g = capi.PeerBuffer(self.cap_r * self.d * item)
+        self.peer_i = capi.PeerBuffer(self.cap_r * 8)
+        handles = [None] * self.world
+        dist.all_gather_object(handles, (self.peer_u.handle, self.peer_g.handle, self.peer_i.handle),
+                               group=self.group)
+        self.peer_u_ptr, self.peer_g_ptr, self.peer_i_ptr = [], [], []
+        for r, (hu, hg, hi) in enumerate(handles):
+            if r == self.rank:
+                self.peer_u_ptr.append(self.peer_u.ptr)
+                self.peer_g_ptr.append(self.peer_g.ptr)
+                self.peer_i_ptr.append(self.peer_i.ptr)
+            else:
+                self.peer_u_ptr.append(capi.peer_open(hu))
+                self.peer_g_ptr.append(capi.peer_open(hg))
+                self.peer_i_ptr.append(capi.peer_open(hi))
+        self.peer_i_ptr_t = torch.tensor(self.peer_i_ptr, dtype=torch.int64, device=self.device)
+        self.peer_u_ptr_t = torch.tensor(self.peer_u_ptr, dtype=torch.int64, device=self.device)
+        self.peer_g_ptr_t = torch.tensor(self.peer_g_ptr, dtype=torch.int64, device=self.device)
+        self.sync_word = torch.zeros(1, dtype=torch.float32, device=self.device)
+        self.row_bytes = self.d * item
+        self.peer = True
+        return True
+
+    def _device_barrier(self):
+        # stream-ordered cross-GPU barrier: every rank's preceding kernels (peer stores) have completed
+        dist.all_reduce(self.sync_word, group=self.group)
 
     # ------------------------------------------------------------------ forward
     def lookup(self, ids, ws, deterministic=False):
@@ -148,26 +197,53 @@ class ShardedTable:
             if self.world > 1:
                 gathered = [torch.empty_like(mine) for _ in range(self.world)]
                 dist.all_gather(gathered, mine, group=self.group)
-                table = torch.stack(gathered).cpu()
+                table_d = torch.stack(gathered)
             else:
-                table = mine.reshape(1, -1).cpu()
+                table_d = mine.reshape(1, -1)
+            table = table_d.cpu()
         g1 = self.world + 1
         ub = table[:, :g1]
         send = (ub[self.rank, 1:] - ub[self.rank, :-1]).tolist()
         recv = (ub[:, self.rank + 1] - ub[:, self.rank]).tolist()
         u = int(ub[self.rank, self.world])
-        recv_local = torch.empty(sum(recv), dtype=torch.int64, device=ids.device)
-        with self._phase("id all-to-all"):
-            all_to_all_rows(recv_local, local[:u], recv, send, self.group)
-        with self._phase("owner gather"):
-            rows = self.ops.lookup(self.shard, recv_local)
-        uvals = torch.empty((u, self.d), dtype=self.dtype, device=ids.device)
-        with self._phase("row all-to-all"):
-            all_to_all_rows(uvals, rows, send, recv, self.group)
+        fused = (self.peer and not deterministic and int(ub[:, self.world].max()) <= self.cap_u and
+                 int((ub[:, 1:] - ub[:, :-1]).sum(dim=0).max()) <= self.cap_r)
+        if fused:
+            ubd = table_d[:, :g1]
+            # rows of lower ranks per owner = this rank's slot in each owner's receive buffers
+            before_me = (ubd[: self.rank, 1:] - ubd[: self.rank, :-1]).sum(dim=0)
+            with self._phase("id scatter to owners (peer stores)"):
+                self.ops.ids_scatter(local, n, bounds, self.peer_i_ptr_t + before_me * 8)
+            with self._phase("barrier"):
+                self._device_barrier()
+            recv_local = self.peer_i.tensor((sum(recv),), torch.int64)
+        else:
+            recv_local = torch.empty(sum(recv), dtype=torch.int64, device=ids.device)
+            with self._phase("id all-to-all"):
+                all_to_all_rows(recv_local, local[:u], recv, send, self.group)
+        if fused:
+            # owner side: gather from the shard straight into every requester's unique-row buffer
+            # scatter maps computed on the device from the gathered split table (no host round trip)
+            seg_start = torch.zeros(g1, dtype=torch.int64, device=ids.device)
+            seg_start[1:] = torch.cumsum(ubd[:, self.rank + 1] - ubd[:, self.rank], dim=0)
+            seg_dst = self.peer_u_ptr_t + ubd[:, self.rank] * self.row_bytes
+            with self._phase("owner gather + peer stores (fused row exchange)"):
+                self.ops.lookup_scatter(self.shard, recv_local, seg_start, seg_dst)
+            with self._phase("barrier"):
+                self._device_barrier()
+            uvals = self.peer_u.tensor((u, self.d), self.dtype)
+            rows = uvals
+        else:
+            with self._phase("owner gather"):
+                rows = self.ops.lookup(self.shard, recv_local)
+            uvals = torch.empty((u, self.d), dtype=self.dtype, device=ids.device)
+            with self._phase("row all-to-all"):
+                all_to_all_rows(uvals, rows, send, recv, self.group)
         with self._phase("expand to batch order"):
             out = self.ops.expand_unique(uvals, n, self.plan_h, ws)
         self.bytes_sent += (u - send[self.rank]) * 8 + (sum(recv) - recv[self.rank]) * self.d * rows.element_size()
-        ctx = {"ids": ids, "n": n, "u": u, "send": send, "recv": recv, "recv_local": recv_local, "ws": ws}
+        ctx = {"ids": ids, "n": n, "u": u, "send": send, "recv": recv, "recv_local": recv_local, "ws": ws,
+               "fused": fused, "bounds": bounds, "ub": ub, "before_me": before_me if fused else None}
         if ebounds is not None:
             eb = table[:, g1:]
             ctx["esend"] = (eb[self.rank, 1:] - eb[self.rank, :-1]).tolist()
@@ -177,7 +253,18 @@ class ShardedTable:
     # ------------------------------------------------------------------ backward + update
     def update(self, ctx, d_out, lr, deterministic=False, adam_state=None, owner_ws=None):
         ids, ws = ctx["ids"], ctx["ws"]
-        if not deterministic:
+        if not deterministic and ctx.get("fused"):
+            # requester side: the local duplicate reduction stores every merged row straight into its owner's
+            # receive buffer, at this rank's slot (ranks before it come first: reference gather-concat order)
+            shard_dst = self.peer_g_ptr_t + ctx["before_me"] * self.row_bytes
+            with self._phase("local MergeAdd + peer stores (fused grad exchange)"):
+                self.ops.merge_scatter(ids, d_out, self.plan_h, ctx["bounds"], shard_dst, ws)
+            with self._phase("barrier"):
+                self._device_barrier()
+            rows = ctx["recv_local"]
+            grads = self.peer_g.tensor((sum(ctx["recv"]), self.d), self.dtype)
+            self.bytes_sent += (ctx["u"] - ctx["send"][self.rank]) * self.row_bytes
+        elif not deterministic:
             with self._phase("local MergeAdd"):
                 merged = self.ops.merge_by_plan(ids, d_out, self.plan_h, ws)[: ctx["u"]]
             grads = torch.empty((sum(ctx["recv"]), self.d), dtype=self.dtype, device=d_out.device)

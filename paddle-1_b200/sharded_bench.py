@@ -32,6 +32,7 @@ def run(args):
     n = int(getattr(args, "ids_per_gpu", 0) or n_base * 16)
     ops = sharded.CudaOps(capi)
     tab = sharded.ShardedTable(v, d, ops, dev)
+    fused = os.environ.get("B200EMB_NO_PEER") is None and tab.enable_peer_exchange(n, 2 * n)
     # random-init shard, in slabs to keep the peak low
     g = torch.Generator(device=dev)
     g.manual_seed(1234 + rank)
@@ -134,7 +135,7 @@ def run(args):
             "config": {"workload": "configs[3]: synthetic 100Mx64 fp32 table row-sharded over %d B200 (owner = id %% G), "
                                    "Zipf(1.1) ids, id/row/grad all-to-all over NVLink (NCCL), sparse SGD" % world,
                        "table": [v, d], "ids_per_gpu_per_step": n, "unique_ids_per_gpu": u_local,
-                       "rows_received_per_gpu": recv_rows, "optimizer": opt, "mode": "fast, dedup before send",
+                       "rows_received_per_gpu": recv_rows, "optimizer": opt, "mode": "fast, dedup before send, " + ("gather and MergeAdd kernels store into peer GPUs over NVLink (no NCCL all-to-all for rows/grads)" if fused else "NCCL all-to-all for rows/grads"),
                        "l2": "inputs rotate over %d batch buffers per GPU (%.0f MB) > 126 MB L2" % (N_ROTATE, N_ROTATE * n * (8 + 8 * d) / 1e6)},
             "roofline": {"bound": "hbm", "achieved": hbm, "peak": peak, "unit": "GB/s", "frac": hbm / peak,
                          "traffic": None, "kernel": "whole sharded step, per GPU (requester + owner side)",

@@ -23,7 +23,7 @@ def core(pkg):
 
 
 def test_kernels_are_registered(core):
-    for op in ("lookup_table", "lookup_table_grad", "sum", "sgd", "adam"):
+    for op in ("lookup_table", "lookup_table_grad", "sum", "sgd", "adam", "adagrad"):
         assert core.registered_kernels(op) == 2        # float + double, CUDAPlace
 
 
@@ -207,3 +207,44 @@ def test_sum_into_dense_accumulates_selected_rows(core):
     # the expectations of selected_rows_functor_test.cc:100-120
     assert out[0, 0] == 6.0 and out[1, 1] == 3.0 and out[4, 6] == 4.0 and out[5, 7] == 5.0
     assert out[6, 1] == 3.0 and out[7, 3] == 6.0 and out[9, 6] == 5.0
+
+
+def test_sparse_adagrad_op(core):
+    # TestSparseAdagradOp.check_with_place (test_adagrad_op.py:87-188) — rows [0, 4, 7, 4], verbatim values
+    import math
+    place = core.CUDAPlace(0)
+    scope = core.Scope()
+    height, rows, row_numel = 10, [0, 4, 7, 4], 12
+    grad_selected_rows = scope.var('Grad').get_selected_rows()
+    grad_selected_rows.set_height(height)
+    grad_selected_rows.set_rows(rows)
+    np_array = np.ones((len(rows), row_numel)).astype("float32")
+    np_array[0, 0] = 2.0
+    np_array[2, 8] = 4.0
+    grad_selected_rows.get_tensor().set(np_array, place)
+    scope.var('Param').get_tensor().set(np.full((height, row_numel), 5.0).astype("float32"), place)
+    scope.var('LearningRate').get_tensor().set(np.full((1), 2.0).astype("float32"), place)
+    scope.var('Moment').get_tensor().set(np.full((height, row_numel), 2.0).astype("float32"), place)
+    adagrad_op = core.Operator("adagrad", Param='Param', Grad='Grad', ParamOut='Param', Moment='Moment',
+                               MomentOut='Moment', LearningRate='LearningRate', epsilon=2.0)
+    adagrad_op.run(scope, place)
+    moment_result_array = np.array(scope.var('Moment').get_tensor())
+    assert moment_result_array[rows[0], 0] == pytest.approx(6.0)
+    assert moment_result_array[rows[0], 2] == pytest.approx(3.0)
+    assert moment_result_array[1, 0] == pytest.approx(2.0)
+    assert moment_result_array[rows[1], 10] == pytest.approx(6.0)      # 2.0 + (1.0 + 1.0)^2
+    assert moment_result_array[rows[3], 4] == pytest.approx(6.0)
+    assert moment_result_array[5, 8] == pytest.approx(2.0)
+    assert moment_result_array[rows[2], 1] == pytest.approx(3.0)
+    assert moment_result_array[rows[2], 8] == pytest.approx(18.0)
+    result_array = np.array(scope.var('Param').get_tensor())
+
+    def get_out(param, lr, grad, m, epsilon):
+        return param - lr * grad / (math.sqrt(m) + epsilon)
+    assert result_array[rows[0], 0] == pytest.approx(get_out(5.0, 2.0, 2.0, 6.0, 2.0), abs=1e-5)
+    assert result_array[rows[0], 2] == pytest.approx(get_out(5.0, 2.0, 1.0, 3.0, 2.0), abs=1e-5)
+    assert result_array[1, 0] == pytest.approx(get_out(5.0, 2.0, 0.0, 2.0, 2.0), abs=1e-5)
+    assert result_array[rows[1], 10] == pytest.approx(get_out(5.0, 2.0, 2.0, 6.0, 2.0), abs=1e-5)   # grad_merge = 1 + 1
+    assert result_array[5, 8] == pytest.approx(get_out(5.0, 2.0, 0.0, 2.0, 2.0), abs=1e-5)
+    assert result_array[rows[2], 1] == pytest.approx(get_out(5.0, 2.0, 1.0, 3.0, 2.0), abs=1e-5)
+    assert result_array[rows[2], 8] == pytest.approx(get_out(5.0, 2.0, 4.0, 18.0, 2.0), abs=1e-5)

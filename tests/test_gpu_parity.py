@@ -405,3 +405,49 @@ def test_config_c2_full_size_step(capi, pkg):
     wr, wt = oracle.merge_add(ids, grad, truth=True)
     assert u == 25223 and np.array_equal(host(r)[:u], wr)
     assert (np.abs(host(val)[:u] - wt) <= FAST_RTOL * l1u + 1e-30).all()
+
+
+# ------------------------------------------------------------------ sparse Adagrad
+def test_sparse_adagrad_golden_g5(capi, goldens):
+    # test_adagrad_op.py:87-188 — rows [0,4,7,4]: the reference's only duplicate-row MergeAdd test
+    import math
+    g = goldens["G5_sparse_adagrad"]
+    grad = np.ones((4, g["row_numel"]), np.float32)
+    for r_, c_, v_ in g["grad_set"]:
+        grad[r_, c_] = v_
+    for flags in (0, DET):
+        p = dev(np.full((g["height"], g["row_numel"]), g["param_fill"], np.float32))
+        m = dev(np.full((g["height"], g["row_numel"]), g["moment_fill"], np.float32))
+        capi.sparse_adagrad(p, m, dev(np.array(g["rows"], np.int64)), dev(grad), dev(np.array([g["lr"]], np.float32)),
+                            g["epsilon"], flags=flags)
+        for r_, c_, v_ in g["expect_moment"]:
+            assert host(m)[r_, c_] == pytest.approx(v_, abs=1e-6)
+        for r_, c_, gr, mm in g["expect_param"]:
+            assert host(p)[r_, c_] == pytest.approx(g["param_fill"] - g["lr"] * gr / (math.sqrt(mm) + g["epsilon"]), abs=1e-5)
+
+
+@pytest.mark.parametrize("case", SHAPES[3:12], ids=lambda c: "n%d_v%d_d%d_%s" % c)
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_sparse_adagrad(capi, case, dtype):
+    n, v, d, dist = case
+    rng = np.random.default_rng(n * 17 + d)
+    rows, grad = make_case(rng, n, v, d, dtype, dist)
+    grad *= dtype(0.01)
+    p0 = (rng.random((v, d)) * 0.1 - 0.05).astype(dtype)
+    m0 = (rng.random((v, d)) * 1e-3).astype(dtype)
+    lr = np.array([0.01], dtype)
+    wp, wm = p0.copy(), m0.copy()
+    oracle.adagrad_sparse(wp, wm, rows, grad, lr, 1e-6)
+    p, m = dev(p0), dev(m0)
+    capi.sparse_adagrad(p, m, dev(rows), dev(grad), dev(lr), 1e-6, flags=DET)
+    assert_bit_equal(host(p), wp, "adagrad det param")
+    assert_bit_equal(host(m), wm, "adagrad det moment")
+    # fast mode == the same functor applied to the fast-mode merged gradient (unique rows -> no reordering left)
+    p, m = dev(p0), dev(m0)
+    capi.sparse_adagrad(p, m, dev(rows), dev(grad), dev(lr), 1e-6)
+    ur, gm, u = capi.merge_add(dev(rows), dev(grad), v)
+    u = int(u.item())
+    ep, em = p0.copy(), m0.copy()
+    oracle.adagrad_sparse(ep, em, host(ur)[:u], host(gm)[:u], lr, 1e-6)
+    assert_bit_equal(host(p), ep, "adagrad fast param")
+    assert_bit_equal(host(m), em, "adagrad fast moment")

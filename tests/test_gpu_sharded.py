@@ -96,7 +96,7 @@ def test_sharded_table_world1_cuda(capi, pkg, deterministic):
         assert (np.abs(after - truth) <= bound + 1e-30).all()
 
 
-def _nccl_worker(rank, world, port, deterministic, q):
+def _nccl_worker(rank, world, port, deterministic, q, peer=False):
     sys.path.insert(0, ROOT)
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     import torch.distributed as dist
@@ -114,8 +114,10 @@ def _nccl_worker(rank, world, port, deterministic, q):
         tab = pkg.sharded.ShardedTable(v, d, pkg.sharded.CudaOps(pkg.capi), dev,
                                        init=lambda rows: torch.from_numpy(full[rows.numpy()]))
         ws = pkg.capi.alloc_workspace(n, d, 4, dev)
+        if peer:
+            assert tab.enable_peer_exchange(n, 2 * n)
         out, ctx = tab.lookup(torch.from_numpy(ids).to(dev), ws, deterministic=deterministic)
-        ok = np.array_equal(out.cpu().numpy(), full[ids])
+        ok = np.array_equal(out.cpu().numpy(), full[ids]) and (ctx["fused"] == (peer and not deterministic))
         tab.update(ctx, torch.from_numpy(dout).to(dev), torch.tensor([0.05], device=dev), deterministic=deterministic)
         after = tab.gather_full_table().cpu().numpy()
         q.put((rank, ok, after if rank == 0 else None, ids, dout))
@@ -123,15 +125,16 @@ def _nccl_worker(rank, world, port, deterministic, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("deterministic", [True, False], ids=["bit-exact", "fast"])
-def test_sharded_table_two_gpus_nccl(capi, deterministic):
+@pytest.mark.parametrize("deterministic,peer", [(True, False), (False, False), (False, True)],
+                         ids=["bit-exact", "fast-nccl", "fast-fused-peer-stores"])
+def test_sharded_table_two_gpus_nccl(capi, deterministic, peer):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
     import torch.multiprocessing as mp
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_nccl_worker, args=(r, 2, port, deterministic, q)) for r in range(2)]
+    procs = [ctx.Process(target=_nccl_worker, args=(r, 2, port, deterministic, q, peer)) for r in range(2)]
     for p in procs:
         p.start()
     got = sorted([q.get(timeout=300) for _ in range(2)], key=lambda t: t[0])
