@@ -451,3 +451,36 @@ def test_sparse_adagrad(capi, case, dtype):
     oracle.adagrad_sparse(ep, em, host(ur)[:u], host(gm)[:u], lr, 1e-6)
     assert_bit_equal(host(p), ep, "adagrad fast param")
     assert_bit_equal(host(m), em, "adagrad fast moment")
+
+
+def test_cluster_sort_opt_in_path_matches_default():
+    """B200EMB_CLUSTER_SORT=1 routes small plans through the single 16-CTA-cluster DSMEM sort
+    (csrc/cluster_sort.cu).  The env var is read once per process, so the check runs in a child process:
+    merged rows and deterministic-mode SGD must equal the oracle bit for bit there too."""
+    import os
+    import subprocess
+    import sys
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = r'''
+import sys, numpy as np, torch
+sys.path.insert(0, %r)
+import oracle, __graft_entry__ as ge
+capi = ge.load_package().capi
+rng = np.random.default_rng(3)
+for n, v, d in [(7, 50, 8), (5000, 4096, 32), (106496, 1000000, 64), (139000, 1 << 27, 16)]:
+    w = np.arange(1, min(v, 200000) + 1, dtype=np.float64) ** -1.1
+    cdf = np.cumsum(w) / w.sum()
+    rows = ((np.searchsorted(cdf, rng.random(n)) * 2654435761 + 12345) %% v).astype(np.int64)
+    grad = (rng.standard_normal((n, d)) * 0.01).astype(np.float32)
+    wr, wv = oracle.merge_add(rows, grad)
+    r, val, u = capi.merge_add(torch.from_numpy(rows).cuda(), torch.from_numpy(grad).cuda(), v, flags=1)
+    u = int(u.item())
+    assert u == len(wr) and np.array_equal(r.cpu().numpy()[:u], wr)
+    assert np.array_equal(val.cpu().numpy()[:u].view(np.uint32), wv.view(np.uint32))
+print("cluster-sort-ok")
+''' % root
+    env = dict(os.environ, B200EMB_CLUSTER_SORT="1")
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "cluster-sort-ok" in out.stdout, out.stderr[-2000:]
