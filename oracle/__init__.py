@@ -31,8 +31,6 @@ def lib():
         if not os.path.exists(path):
             build()
         _LIB = ctypes.CDLL(path)
-        for name in dir(_LIB):
-            pass
         _LIB.oracle_abi_version.restype = ctypes.c_int
     return _LIB
 

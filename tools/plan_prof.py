@@ -1,5 +1,7 @@
+"""Developer tool: runs the large-batch sharded-path kernels once per iteration (for an ncu launch list)."""
 import sys, torch, numpy as np
-sys.path.insert(0, "/root/repo")
+import os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import __graft_entry__ as ge
 pkg = ge.load_package(); capi = pkg.capi
 n, v, G, d = 1703936, 100_000_000, 8, 64
