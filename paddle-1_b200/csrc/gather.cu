@@ -6,6 +6,7 @@
 // flight per group, and the grid covers every SM at full occupancy.  Table loads allocate in
 // L1/L2 (hot Zipf rows are re-read), output stores stream past L1.
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "internal.h"
@@ -89,6 +90,84 @@ k_gather(const T* __restrict__ table, const int64_t* __restrict__ ids, T* __rest
   if (bad && status) atomicOr(status, 1);
 }
 
+
+// ---- wide rows: TMA bulk row copies ---------------------------------------------------------------
+// For rows of 512 B and more a lane does not touch the data at all: it asks the TMA unit to copy its row
+// global -> shared (cp.async.bulk + mbarrier complete_tx) and, once the warp's batch has landed, shared ->
+// global (bulk store, bulk_group).  One lane = one row, up to 32 rows in flight per warp, no registers
+// spent on payload.  Padding / out-of-range rows are zero-filled in shared memory by their lane.
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               :: "r"(smem_u32(dst_smem)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* dst, const void* src_smem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+               :: "l"(dst), "r"(smem_u32(src_smem)), "r"(bytes) : "memory");
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kBlock)
+k_gather_bulk(const T* __restrict__ table, const int64_t* __restrict__ ids, T* __restrict__ out, int64_t n,
+              int64_t height, int d, int64_t padding_idx, int32_t* status, int slots) {
+  constexpr int kWarps = kBlock / 32;
+  extern __shared__ __align__(128) unsigned char bulk_smem[];   // [kWarps][slots][row bytes]
+  __shared__ __align__(8) uint64_t bars[kWarps];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t row_bytes = static_cast<uint32_t>(d) * sizeof(T);
+  if (lane == 0) mbar_init(&bars[warp], 1);
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  __syncthreads();
+  unsigned char* my_slot = bulk_smem + (static_cast<size_t>(warp) * slots + lane) * row_bytes;
+  const int64_t warp_global = static_cast<int64_t>(blockIdx.x) * kWarps + warp;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * kWarps * slots;
+  uint32_t parity = 0;
+  bool bad = false;
+  for (int64_t base = warp_global * slots; base < n; base += stride) {
+    const int64_t k = base + lane;
+    const bool live = lane < slots && k < n;
+    const int64_t id = live ? ids[k] : 0;
+    const bool pad = padding_idx != -1 && id == padding_idx;
+    const bool ok = id >= 0 && id < height;
+    const bool copy = live && !pad && ok;
+    bad |= live && !pad && !ok;
+    const uint32_t cnt = __popc(__ballot_sync(0xffffffffu, copy));
+    if (lane == 0 && cnt > 0) mbar_expect_tx(&bars[warp], cnt * row_bytes);
+    __syncwarp();
+    if (copy) {
+      bulk_g2s(my_slot, table + id * d, row_bytes, &bars[warp]);
+    } else if (live) {
+      for (uint32_t b = 0; b < row_bytes; b += 16) *reinterpret_cast<int4*>(my_slot + b) = make_int4(0, 0, 0, 0);
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // zero fills visible to the bulk store
+    if (cnt > 0) {
+      mbar_wait(&bars[warp], parity);
+      parity ^= 1u;
+    }
+    __syncwarp();
+    if (live) bulk_s2g(out + k * d, my_slot, row_bytes);
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // slot may be overwritten next round
+    __syncwarp();
+  }
+  if (bad && status) atomicOr(status, 1);
+}
+
 }  // namespace
 
 template <typename T>
@@ -97,6 +176,24 @@ cudaError_t launch_gather(const T* table, int64_t height, int64_t d, const int64
                           const int64_t* seg_start, T* const* seg_dst, int segs) {
   if (n == 0) return cudaSuccess;
   const bool aligned = is_aligned16(table) && (segs > 0 || is_aligned16(out));
+  // wide rows (>= 512 B): TMA bulk row copies — opt-in (B200EMB_GATHER_BULK=1).  Measured on B200 the
+  // un-pipelined bulk path loses to the 128-bit LDG/STG path, which already runs near the HBM roofline for
+  // wide rows (C5, 1 KB rows: 1966 us vs 1436 us; C3, 512 B rows: 84 us vs 79 us), so LDG stays the default.
+  const int64_t row_bytes = d * static_cast<int64_t>(sizeof(T));
+  static const bool bulk_on = std::getenv("B200EMB_GATHER_BULK") != nullptr;
+  if (bulk_on && segs == 0 && aligned && row_bytes >= 512 && row_bytes % 16 == 0 && row_bytes <= 12288) {
+    constexpr int kWarps = kBlock / 32;
+    const int slots = static_cast<int>(std::min<int64_t>(32, (96 * 1024) / (kWarps * row_bytes)));
+    const size_t smem = static_cast<size_t>(kWarps) * slots * row_bytes;
+    cudaError_t e = cudaFuncSetAttribute(k_gather_bulk<T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(smem));
+    if (e != cudaSuccess) return e;
+    const int64_t want = ceil_div(n, static_cast<int64_t>(kWarps) * slots);
+    const int grid = static_cast<int>(std::min<int64_t>(want, 148 * 2));
+    k_gather_bulk<T><<<grid, kBlock, smem, s>>>(table, ids, out, n, height, static_cast<int>(d), padding_idx,
+                                                status, slots);
+    return cudaGetLastError();
+  }
   cudaError_t err = cudaSuccess;
   dispatch_row_shape<T>(d, aligned, [&]<int LPR, int NV, bool VEC>() {
     constexpr int kGroups = kBlock / LPR;

@@ -484,3 +484,37 @@ print("cluster-sort-ok")
     env = dict(os.environ, B200EMB_CLUSTER_SORT="1")
     out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "cluster-sort-ok" in out.stdout, out.stderr[-2000:]
+
+
+def test_tma_bulk_gather_opt_in_path_is_bit_exact():
+    """B200EMB_GATHER_BULK=1 routes rows of >= 512 B through the TMA bulk-copy gather (cp.async.bulk +
+    mbarrier, csrc/gather.cu k_gather_bulk).  Checked in a child process (env var is read once)."""
+    import os
+    import subprocess
+    import sys
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = r'''
+import sys, numpy as np, torch
+sys.path.insert(0, %r)
+import oracle, __graft_entry__ as ge
+capi = ge.load_package().capi
+rng = np.random.default_rng(5)
+for d, dtype in [(128, np.float32), (256, np.float32), (1028, np.float32), (64, np.float64), (3000, np.float32)]:
+    v, n = 2000, 70001
+    table = rng.standard_normal((v, d)).astype(dtype)
+    ids = rng.integers(0, v, size=n).astype(np.int64)
+    ids[5] = v + 3
+    pad = int(ids[11])
+    status = capi.new_status()
+    got = capi.lookup_table(torch.from_numpy(table).cuda(), torch.from_numpy(ids).cuda(), pad, status=status).cpu().numpy()
+    want_ids = ids.copy(); want_ids[5] = pad
+    want = oracle.lookup_table(table, want_ids, pad)
+    assert np.array_equal(got, want), d
+    assert int(status.item()) & 1
+print("bulk-gather-ok")
+''' % root
+    env = dict(os.environ, B200EMB_GATHER_BULK="1")
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "bulk-gather-ok" in out.stdout, out.stderr[-2000:]

@@ -48,7 +48,22 @@ def _worker(rank, world, port, deterministic, results):
         fwd_ok = np.array_equal(out.numpy(), full[ids])
         tab.update(ctx, torch.from_numpy(dout), torch.tensor([0.05]), deterministic=deterministic)
         after = tab.gather_full_table().numpy()
+        # shard-aware checkpoint in the reference's LoDTensor format: one [V, D] file in global row order
+        import importlib
+        import tempfile
+        ck = importlib.import_module("paddle1_b200.checkpoint")
+        path = os.path.join(tempfile.gettempdir(), "b200emb_ckpt_%d" % port)
+        ck.save_sharded(path, tab.shard, V, rank, world)
+        dist.barrier()
         if rank == 0:
+            with open(path, "rb") as f:
+                saved, _ = ck.read_lod_tensor(f)
+            fwd_ok = fwd_ok and np.array_equal(saved, after)
+        back, _ = ck.load_sharded(path, rank, world, "cpu")
+        fwd_ok = fwd_ok and torch.equal(back, tab.shard)
+        dist.barrier()
+        if rank == 0:
+            os.remove(path)
             results.put((fwd_ok, after))
         else:
             results.put((fwd_ok, None))
