@@ -127,6 +127,22 @@ int b200emb_gather_sorted_f32(const float* value, int64_t n, int64_t d, int64_t 
 int b200emb_gather_sorted_f64(const double* value, int64_t n, int64_t d, int64_t plan_height,
                               void* workspace, size_t workspace_bytes, double* out, void* stream);
 
+/* split_ids / merge_ids with the reference's exact semantics (both are CPU-only in the
+ * reference and PADDLE_THROW on GPU: split_ids_op.h:30-32, merge_ids_op.h:30-32).
+ *   split_ids (LoDTensor branch, split_ids_op.h:36-58): out_ids = ids grouped by id % shard_num, input
+ *     order and duplicates kept inside a shard; bounds[g] = first position of shard g, bounds[shard_num] =
+ *     number of in-range ids (device int64[shard_num+1]).  The workspace keeps the permutation.
+ *   merge_ids (merge_ids_op.h:63-87): x = the shards' row blocks laid out shard after shard ([n, d]);
+ *     out[i,:] = the next unused row of shard ids[i] % shard_num — needs the workspace of split_ids on the
+ *     same ids. */
+int b200emb_split_ids(const int64_t* ids, int64_t n, int64_t height, int64_t shard_num, int64_t* out_ids,
+                      int64_t* bounds, void* workspace, size_t workspace_bytes, int32_t* status,
+                      void* stream);
+int b200emb_merge_ids_f32(const float* x, int64_t n, int64_t d, int64_t shard_num, void* workspace,
+                          size_t workspace_bytes, float* out, void* stream);
+int b200emb_merge_ids_f64(const double* x, int64_t n, int64_t d, int64_t shard_num, void* workspace,
+                          size_t workspace_bytes, double* out, void* stream);
+
 /* Fused compute + exchange for the row-sharded path (no counterpart in the reference, whose
  * multi-device SelectedRows path copies whole blocks with cudaMemcpyPeer: memory/memcpy.cc:65-72).
  * The destinations are device pointers that may live on OTHER GPUs of the box (peer-mapped, e.g.

@@ -33,6 +33,7 @@ EXPORTS = [
     "b200emb_plan_unique_rows", "b200emb_expand_unique_f32", "b200emb_expand_unique_f64",
     "b200emb_gather_sorted_f32", "b200emb_gather_sorted_f64",
     "b200emb_lookup_table_scatter_f32", "b200emb_merge_add_scatter_f32", "b200emb_segment_scatter_i64",
+    "b200emb_split_ids", "b200emb_merge_ids_f32", "b200emb_merge_ids_f64",
     "b200emb_peer_alloc", "b200emb_peer_open", "b200emb_peer_close", "b200emb_peer_free",
 ]
 
@@ -391,3 +392,29 @@ def sparse_adagrad(param, moment, rows, grad, lr, epsilon=1e-6, workspace=None, 
               ctypes.c_size_t(workspace.numel()), ctypes.c_uint(flags), _ptr(status), _stream()),
            "sparse_adagrad")
     return param
+
+
+def split_ids(ids, height, shard_num, workspace, status=None):
+    """Reference split_ids on a LoDTensor of ids: (out_ids[n] grouped by id % shard_num in input order,
+    bounds[shard_num+1]).  The workspace keeps the permutation for merge_ids."""
+    _need_cuda(ids, workspace, status)
+    n = ids.numel()
+    out = torch.empty(max(n, 1), dtype=torch.int64, device=ids.device)
+    bounds = torch.zeros(shard_num + 1, dtype=torch.int64, device=ids.device)
+    _check(lib().b200emb_split_ids(_ptr(ids), ctypes.c_int64(n), ctypes.c_int64(height), ctypes.c_int64(shard_num),
+                                   _ptr(out), _ptr(bounds), _ptr(workspace), ctypes.c_size_t(workspace.numel()),
+                                   _ptr(status), _stream()), "split_ids")
+    return out[:n], bounds
+
+
+def merge_ids(x, shard_num, workspace, out=None):
+    """Reference merge_ids: rows of the shards (concatenated shard after shard) back to the order of the ids
+    that split_ids was run on with this workspace."""
+    _need_cuda(x, workspace, out)
+    n, d = x.shape
+    if out is None:
+        out = torch.empty_like(x)
+    fn = getattr(lib(), "b200emb_merge_ids_" + _sfx(x.dtype))
+    _check(fn(_ptr(x), ctypes.c_int64(n), ctypes.c_int64(d), ctypes.c_int64(shard_num), _ptr(workspace),
+              ctypes.c_size_t(workspace.numel()), _ptr(out), _stream()), "merge_ids")
+    return out

@@ -205,7 +205,7 @@ extern "C++" {
 namespace {
 template <typename T>
 int run_permute(const T* src, int64_t n, int64_t d, int64_t plan_height, void* workspace,
-                size_t workspace_bytes, T* out, bool unique, void* stream) {
+                size_t workspace_bytes, T* out, int mode, void* stream) {
   int rc = check_sizes(n, d, plan_height);
   if (rc != B200EMB_OK) return rc;
   if (n == 0) return B200EMB_OK;
@@ -216,7 +216,7 @@ int run_permute(const T* src, int64_t n, int64_t d, int64_t plan_height, void* w
   char* ws = static_cast<char*>(workspace);
   const SortedPlan plan = plan_view(n, plan_height, ws, L);
   cudaError_t e = launch_permute_rows<T>(src, plan, reinterpret_cast<const uint32_t*>(ws + L.off_uidx), n,
-                                         d, out, unique, static_cast<cudaStream_t>(stream));
+                                         d, out, mode, static_cast<cudaStream_t>(stream));
   return e == cudaSuccess ? B200EMB_OK : fail_cuda(e);
 }
 }  // namespace
@@ -224,19 +224,65 @@ int run_permute(const T* src, int64_t n, int64_t d, int64_t plan_height, void* w
 
 int b200emb_expand_unique_f32(const float* unique_values, int64_t n, int64_t d, int64_t plan_height,
                               void* workspace, size_t workspace_bytes, float* out, void* stream) {
-  return run_permute<float>(unique_values, n, d, plan_height, workspace, workspace_bytes, out, true, stream);
+  return run_permute<float>(unique_values, n, d, plan_height, workspace, workspace_bytes, out, 1, stream);
 }
 int b200emb_expand_unique_f64(const double* unique_values, int64_t n, int64_t d, int64_t plan_height,
                               void* workspace, size_t workspace_bytes, double* out, void* stream) {
-  return run_permute<double>(unique_values, n, d, plan_height, workspace, workspace_bytes, out, true, stream);
+  return run_permute<double>(unique_values, n, d, plan_height, workspace, workspace_bytes, out, 1, stream);
 }
 int b200emb_gather_sorted_f32(const float* value, int64_t n, int64_t d, int64_t plan_height,
                               void* workspace, size_t workspace_bytes, float* out, void* stream) {
-  return run_permute<float>(value, n, d, plan_height, workspace, workspace_bytes, out, false, stream);
+  return run_permute<float>(value, n, d, plan_height, workspace, workspace_bytes, out, 0, stream);
 }
 int b200emb_gather_sorted_f64(const double* value, int64_t n, int64_t d, int64_t plan_height,
                               void* workspace, size_t workspace_bytes, double* out, void* stream) {
-  return run_permute<double>(value, n, d, plan_height, workspace, workspace_bytes, out, false, stream);
+  return run_permute<double>(value, n, d, plan_height, workspace, workspace_bytes, out, 0, stream);
+}
+
+// ---- split_ids / merge_ids with the reference's exact (duplicate-keeping) semantics ---------------
+int b200emb_split_ids(const int64_t* ids, int64_t n, int64_t height, int64_t shard_num, int64_t* out_ids,
+                      int64_t* bounds, void* workspace, size_t workspace_bytes, int32_t* status,
+                      void* stream) {
+  int rc = check_sizes(n, 1, height);
+  if (rc != B200EMB_OK) return rc;
+  if (shard_num < 1 || shard_num > 65536 || !bounds) return B200EMB_E_INVALID;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (n == 0) {
+    cudaError_t e = cudaMemsetAsync(bounds, 0, sizeof(int64_t) * (shard_num + 1), s);
+    return e == cudaSuccess ? B200EMB_OK : fail_cuda(e);
+  }
+  if (!ids || !out_ids) return B200EMB_E_INVALID;
+  const Workspace L = make_workspace(n, 1, 4);
+  rc = check_workspace(workspace, workspace_bytes, L);
+  if (rc != B200EMB_OK) return rc;
+  char* ws = static_cast<char*>(workspace);
+  KeyMap km;
+  km.shards = static_cast<uint32_t>(shard_num);
+  km.shard_height = 1;
+  km.raw_height = static_cast<uint32_t>(height);
+  km.owner_only = true;
+  SortedPlan plan;
+  cudaError_t e = launch_plan(ids, n, shard_num, ws, L, status, s, &plan, &km);   // stable partition by owner
+  if (e != cudaSuccess) return fail_cuda(e);
+  // owners present (unique keys) go to out_ids[0..U) for a moment; the gather below overwrites them
+  e = launch_head_scan(plan, n, static_cast<uint32_t>(shard_num), ws, L, out_ids, nullptr, s);
+  if (e != cudaSuccess) return fail_cuda(e);
+  e = launch_shard_split(out_ids, plan, ws, L, static_cast<int>(shard_num), 1, n,
+                         static_cast<uint32_t>(shard_num), nullptr, bounds, nullptr, s);
+  if (e != cudaSuccess) return fail_cuda(e);
+  e = launch_permute_rows<double>(reinterpret_cast<const double*>(ids), plan,
+                                  reinterpret_cast<const uint32_t*>(ws + L.off_uidx), n, 1,
+                                  reinterpret_cast<double*>(out_ids), 0, s);      // 8-byte bit copies
+  return e == cudaSuccess ? B200EMB_OK : fail_cuda(e);
+}
+
+int b200emb_merge_ids_f32(const float* x, int64_t n, int64_t d, int64_t shard_num, void* workspace,
+                          size_t workspace_bytes, float* out, void* stream) {
+  return run_permute<float>(x, n, d, shard_num, workspace, workspace_bytes, out, 2, stream);
+}
+int b200emb_merge_ids_f64(const double* x, int64_t n, int64_t d, int64_t shard_num, void* workspace,
+                          size_t workspace_bytes, double* out, void* stream) {
+  return run_permute<double>(x, n, d, shard_num, workspace, workspace_bytes, out, 2, stream);
 }
 
 // ---- peer-store variants for the sharded path (destinations may be other GPUs' memory) ----------

@@ -66,10 +66,12 @@ struct SortedPlan {      // device pointers into the workspace after plan_rows
 // shards * shard_height.
 struct KeyMap {
   uint32_t shards = 1, shard_height = 0, raw_height = 0;
+  bool owner_only = false;   // key = id % shards: a stable partition by owner (split_ids on a LoDTensor)
 #if defined(__CUDACC__)
   __host__ __device__
 #endif
   uint32_t operator()(uint32_t id) const {
+    if (owner_only) return id % shards;
     return shards > 1 ? (id % shards) * shard_height + id / shards : id;
   }
 };
@@ -129,8 +131,9 @@ cudaError_t launch_shard_split(const int64_t* ukeys, const SortedPlan& plan, cha
                                int64_t* local_rows, cudaStream_t s);
 cudaError_t launch_segment_scatter_i64(const int64_t* src, int64_t n_upper, const int64_t* bounds,
                                        int64_t* const* dst, int segs, cudaStream_t s);
+// mode 0: out[e] = src[perm[e]]   1: out[perm[e]] = src[uidx[e]]   2: out[perm[e]] = src[e]
 template <typename T>
 cudaError_t launch_permute_rows(const T* src, const SortedPlan& plan, const uint32_t* uidx, int64_t n,
-                                int64_t d, T* out, bool unique, cudaStream_t s);
+                                int64_t d, T* out, int mode, cudaStream_t s);
 
 }  // namespace b200emb

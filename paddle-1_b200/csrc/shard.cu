@@ -69,8 +69,8 @@ k_segment_scatter_i64(const int64_t* __restrict__ src, const int64_t* __restrict
   }
 }
 
-// out[perm[e], :] = src[uidx[e], :]  (UNIQUE)   or   out[e, :] = src[perm[e], :]  (!UNIQUE)
-template <typename T, int LPR, int NV, bool VEC, bool UNIQUE>
+// MODE 0: out[e, :] = src[perm[e], :]   1: out[perm[e], :] = src[uidx[e], :]   2: out[perm[e], :] = src[e, :]
+template <typename T, int LPR, int NV, bool VEC, int MODE>
 __global__ void __launch_bounds__(kBlock, 4)
 k_permute_rows(const T* __restrict__ src, const uint32_t* __restrict__ perm,
                const uint32_t* __restrict__ uidx, int n, int d, T* __restrict__ out) {
@@ -87,8 +87,11 @@ k_permute_rows(const T* __restrict__ src, const uint32_t* __restrict__ perm,
     for (int r = 0; r < kRows; ++r) {
       const int e = base + r * num_groups;
       live[r] = e < n;
-      if (UNIQUE) {
+      if (MODE == 1) {
         from[r] = live[r] ? uidx[e] : 0;
+        to[r] = live[r] ? perm[e] : 0;
+      } else if (MODE == 2) {
+        from[r] = e;
         to[r] = live[r] ? perm[e] : 0;
       } else {
         from[r] = live[r] ? perm[e] : 0;
@@ -139,27 +142,30 @@ cudaError_t launch_segment_scatter_i64(const int64_t* src, int64_t n_upper, cons
 
 template <typename T>
 cudaError_t launch_permute_rows(const T* src, const SortedPlan& plan, const uint32_t* uidx, int64_t n,
-                                int64_t d, T* out, bool unique, cudaStream_t s) {
+                                int64_t d, T* out, int mode, cudaStream_t s) {
   if (n == 0) return cudaSuccess;
   const bool aligned = is_aligned16(src) && is_aligned16(out);
   cudaError_t err = cudaSuccess;
   dispatch_row_shape<T>(d, aligned, [&]<int LPR, int NV, bool VEC>() {
     constexpr int kGroups = kBlock / LPR;
     const int grid = static_cast<int>(std::min<int64_t>(ceil_div(n, kGroups), 148 * 4));
-    if (unique)
-      k_permute_rows<T, LPR, NV, VEC, true><<<grid, kBlock, 0, s>>>(src, plan.perm, uidx, static_cast<int>(n),
-                                                                    static_cast<int>(d), out);
+    if (mode == 1)
+      k_permute_rows<T, LPR, NV, VEC, 1><<<grid, kBlock, 0, s>>>(src, plan.perm, uidx, static_cast<int>(n),
+                                                                 static_cast<int>(d), out);
+    else if (mode == 2)
+      k_permute_rows<T, LPR, NV, VEC, 2><<<grid, kBlock, 0, s>>>(src, plan.perm, uidx, static_cast<int>(n),
+                                                                 static_cast<int>(d), out);
     else
-      k_permute_rows<T, LPR, NV, VEC, false><<<grid, kBlock, 0, s>>>(src, plan.perm, uidx, static_cast<int>(n),
-                                                                     static_cast<int>(d), out);
+      k_permute_rows<T, LPR, NV, VEC, 0><<<grid, kBlock, 0, s>>>(src, plan.perm, uidx, static_cast<int>(n),
+                                                                 static_cast<int>(d), out);
     err = cudaGetLastError();
   });
   return err;
 }
 
 template cudaError_t launch_permute_rows<float>(const float*, const SortedPlan&, const uint32_t*, int64_t,
-                                                int64_t, float*, bool, cudaStream_t);
+                                                int64_t, float*, int, cudaStream_t);
 template cudaError_t launch_permute_rows<double>(const double*, const SortedPlan&, const uint32_t*, int64_t,
-                                                 int64_t, double*, bool, cudaStream_t);
+                                                 int64_t, double*, int, cudaStream_t);
 
 }  // namespace b200emb

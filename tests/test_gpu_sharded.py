@@ -159,3 +159,31 @@ def test_sharded_table_two_gpus_nccl(capi, deterministic, peer):
         bound = 1e-6 * np.abs(base)
         bound[rows] += 1e-6 * 0.05 * l1
         assert (np.abs(after - truth) <= bound + 1e-30).all()
+
+
+def test_split_ids_merge_ids_reference_semantics(capi, goldens):
+    """Device split_ids / merge_ids against the reference's own test vectors (G9: test_split_ids_op.py:26-38,
+    test_merge_ids_op.py:22-34) and against the oracle on random ids."""
+    g = goldens["G9_split_merge_ids"]
+    ids = np.array(g["ids"], np.int64)
+    ws = capi.alloc_workspace(ids.size, 2)
+    out, bounds = capi.split_ids(torch.from_numpy(ids).cuda(), 100, g["shard_num"], ws)
+    b = bounds.cpu().tolist()
+    got = [out.cpu().numpy()[b[s]:b[s + 1]].tolist() for s in range(g["shard_num"])]
+    assert got == g["expect_shards"]
+    x = np.concatenate([np.array(x_, np.float32).reshape(-1, 2) for x_ in g["merge_x"]])
+    merged = capi.merge_ids(torch.from_numpy(x).cuda(), g["shard_num"], ws).cpu().numpy()
+    assert np.array_equal(merged, np.array(g["merge_expect"], np.float32))
+    rng = np.random.default_rng(9)
+    for n, v, shards, d in [(5000, 977, 4, 16), (200000, 1 << 20, 8, 64), (3000, 50, 3, 5)]:
+        ids = _zipf_ids(rng, n, v)
+        ws = capi.alloc_workspace(n, d)
+        out, bounds = capi.split_ids(torch.from_numpy(ids).cuda(), v, shards, ws)
+        want = oracle.split_ids(ids, shards)
+        b = bounds.cpu().tolist()
+        for s in range(shards):
+            assert np.array_equal(out.cpu().numpy()[b[s]:b[s + 1]], want[s])
+        blocks = [rng.standard_normal((len(w), d)).astype(np.float32) for w in want]
+        x = np.concatenate(blocks)
+        merged = capi.merge_ids(torch.from_numpy(x).cuda(), shards, ws).cpu().numpy()
+        assert np.array_equal(merged, oracle.merge_ids(ids, blocks))
