@@ -98,11 +98,17 @@ def radix_passes(n, height):
     return (bits + maxb - 1) // maxb
 
 
+HEAD_SCAN_KERNELS = 2   # k_head_count + k_head_write
+
+
 def plan_kernel_count(n, height):
-    """Kernels one sort plan launches: prepare + radix passes (1 with B200EMB_CLUSTER_SORT set)."""
+    """Kernels one sort plan launches: prepare + radix passes, plus one column scan per pass above
+    64 tiles of 2048 ids (1 with B200EMB_CLUSTER_SORT set).  The run-length head scan that follows
+    a plan (inside plan_unique_rows / the first consumer) is HEAD_SCAN_KERNELS more."""
     if 0 < n <= 16 * 8704 and "B200EMB_CLUSTER_SORT" in os.environ:
         return 1
-    return 1 + radix_passes(n, height)
+    passes = radix_passes(n, height)
+    return 1 + passes * (1 if (n + 2047) // 2048 <= 64 else 2)
 
 
 def workspace_bytes(n, d, elem_size=4):

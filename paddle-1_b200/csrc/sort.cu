@@ -318,11 +318,12 @@ constexpr int kDirectMaxTiles = 64;
 template <int BITS>
 __global__ void __launch_bounds__(kSortThreads, 4)
 k_prepare_direct(const int64_t* __restrict__ rows, int n, uint32_t height, KeyMap km, int passes,
-                 uint32_t* __restrict__ keys, uint32_t* __restrict__ hmat, int32_t* status) {
+                 uint32_t* __restrict__ keys, uint32_t* __restrict__ hmat, size_t per_pass,
+                 int32_t* status) {
   constexpr int kBins = 1 << BITS;
   __shared__ uint32_t sh[kBins];
   const int tid = threadIdx.x, lane = tid & 31;
-  const int tile = blockIdx.x, tiles = gridDim.x;
+  const int tile = blockIdx.x;
   for (int i = tid; i < kBins; i += kSortThreads) sh[i] = 0;
   __syncthreads();
   bool bad = false;
@@ -346,12 +347,77 @@ k_prepare_direct(const int64_t* __restrict__ rows, int n, uint32_t height, KeyMa
   for (int i = tid; i < kBins; i += kSortThreads) {
     hmat[static_cast<size_t>(tile) * kBins + i] = sh[i];
     for (int p = 1; p < passes; ++p)
-      hmat[(static_cast<size_t>(p) * tiles + tile) * kBins + i] = 0;
+      hmat[p * per_pass + static_cast<size_t>(tile) * kBins + i] = 0;
   }
   if (bad && status) atomicOr(status, 2);
 }
 
-template <int BITS, bool HAS_PERM_IN>
+// ---- larger batches: the same matrix, scanned by its own small launch -----------------------
+// Reading a whole column block per tile is quadratic in the tile count, and a chained look-back
+// makes every resident tile poll its predecessors' counters (measured: 12-17k cycles of waiting
+// per tile at 832 tiles).  Instead k_colscan turns H[pass] into exclusive prefixes over tiles in
+// place — one CTA per 8 bins, a warp instruction covers 4 tiles x 8 bins (32-byte sectors),
+// 32 warps split the tiles — and leaves the column totals in row `tiles`.  The pass kernel then
+// reads exactly two rows.  Launches per plan: 1 + 2*passes, no flags, no polling, no memset.
+constexpr int kColscanBins = 8;
+constexpr int kColscanThreads = 1024;
+
+__global__ void __launch_bounds__(kColscanThreads)
+k_colscan(uint32_t* __restrict__ hmat, int tiles, int bins) {
+  constexpr int kWarps = kColscanThreads / 32;
+  constexpr int kU = 4;                               // row groups in flight per thread
+  __shared__ uint32_t s_tot[kWarps][kColscanBins];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int b = lane & 7, r = lane >> 3;
+  const int groups = (tiles + 3) / 4;                  // groups of 4 consecutive tiles
+  const int per_warp = (groups + kWarps - 1) / kWarps;
+  const int g_lo = warp * per_warp, g_hi = min(groups, g_lo + per_warp);
+  uint32_t* col = hmat + blockIdx.x * kColscanBins + b;
+  uint32_t sum = 0;
+  for (int g = g_lo; g < g_hi; g += kU) {
+    uint32_t v[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int t = (g + u) * 4 + r;
+      v[u] = (g + u < g_hi && t < tiles) ? col[static_cast<size_t>(t) * bins] : 0u;
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) sum += v[u];
+  }
+  sum += __shfl_xor_sync(0xffffffffu, sum, 8);
+  sum += __shfl_xor_sync(0xffffffffu, sum, 16);
+  if (r == 0) s_tot[warp][b] = sum;
+  __syncthreads();
+  uint32_t run = 0, total = 0;
+#pragma unroll 8
+  for (int w = 0; w < kWarps; ++w) {
+    const uint32_t c = s_tot[w][b];
+    run += w < warp ? c : 0u;
+    total += c;
+  }
+  for (int g = g_lo; g < g_hi; g += kU) {
+    uint32_t v[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int t = (g + u) * 4 + r;
+      v[u] = (g + u < g_hi && t < tiles) ? col[static_cast<size_t>(t) * bins] : 0u;
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const uint32_t v0 = __shfl_sync(0xffffffffu, v[u], b);
+      const uint32_t v1 = __shfl_sync(0xffffffffu, v[u], 8 + b);
+      const uint32_t v2 = __shfl_sync(0xffffffffu, v[u], 16 + b);
+      const uint32_t v3 = __shfl_sync(0xffffffffu, v[u], 24 + b);
+      const uint32_t pre = (r > 0 ? v0 : 0u) + (r > 1 ? v1 : 0u) + (r > 2 ? v2 : 0u);
+      const int t = (g + u) * 4 + r;
+      if (g + u < g_hi && t < tiles) col[static_cast<size_t>(t) * bins] = run + pre;
+      run += v0 + v1 + v2 + v3;
+    }
+  }
+  if (warp == 0 && r == 0) col[static_cast<size_t>(tiles) * bins] = total;
+}
+
+template <int BITS, bool HAS_PERM_IN, bool SCANNED>
 __global__ void __launch_bounds__(kSortThreads, 4)   // <= 64 registers: fits beside the row kernels on an SM
 k_radix_pass_direct(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ perm_in,
                     uint32_t* __restrict__ keys_out, uint32_t* __restrict__ perm_out, int n,
@@ -378,30 +444,35 @@ k_radix_pass_direct(const uint32_t* __restrict__ keys_in, const uint32_t* __rest
     key[j] = valid ? keys_in[idx] : 0u;
     pm[j] = valid ? (HAS_PERM_IN ? perm_in[idx] : static_cast<uint32_t>(idx)) : 0u;
   }
-  // column block of this thread's K bins: prefix over earlier tiles + totals over all tiles
+  // this thread's K bins: prefix over earlier tiles + totals over all tiles
   uint32_t excl[K], total[K];
+  if constexpr (SCANNED) {   // k_colscan left the prefixes in row `tile`, the totals in row `tiles`
+    ld_cg_vec<K>(hmat + static_cast<size_t>(tile) * kBins + tid * K, excl);
+    ld_cg_vec<K>(hmat + static_cast<size_t>(tiles) * kBins + tid * K, total);
+  } else {
 #pragma unroll
-  for (int k = 0; k < K; ++k) { excl[k] = 0; total[k] = 0; }
-  constexpr int kU = K >= 4 ? 26 : 32;   // rows of the matrix in flight per round trip
-  for (int t0 = 0; t0 < tiles; t0 += kU) {
-    uint32_t v[kU][K];
+    for (int k = 0; k < K; ++k) { excl[k] = 0; total[k] = 0; }
+    constexpr int kU = K >= 4 ? 26 : 32;   // rows of the matrix in flight per round trip
+    for (int t0 = 0; t0 < tiles; t0 += kU) {
+      uint32_t v[kU][K];
 #pragma unroll
-    for (int u = 0; u < kU; ++u) {
-      const int t = t0 + u;
-      if (t < tiles) {
-        ld_cg_vec<K>(hmat + static_cast<size_t>(t) * kBins + tid * K, v[u]);
-      } else {
+      for (int u = 0; u < kU; ++u) {
+        const int t = t0 + u;
+        if (t < tiles) {
+          ld_cg_vec<K>(hmat + static_cast<size_t>(t) * kBins + tid * K, v[u]);
+        } else {
 #pragma unroll
-        for (int k = 0; k < K; ++k) v[u][k] = 0;
+          for (int k = 0; k < K; ++k) v[u][k] = 0;
+        }
       }
+#pragma unroll
+      for (int u = 0; u < kU; ++u)
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+          total[k] += v[u][k];
+          excl[k] += (t0 + u < tile) ? v[u][k] : 0u;
+        }
     }
-#pragma unroll
-    for (int u = 0; u < kU; ++u)
-#pragma unroll
-      for (int k = 0; k < K; ++k) {
-        total[k] += v[u][k];
-        excl[k] += (t0 + u < tile) ? v[u][k] : 0u;
-      }
   }
   __syncthreads();
   // stable rank inside the warp: items are ordered (j, lane) == ascending idx
@@ -471,77 +542,108 @@ k_radix_pass_direct(const uint32_t* __restrict__ keys_in, const uint32_t* __rest
   }
 }
 
-__global__ void __launch_bounds__(256)
-k_head_scan(const uint32_t* __restrict__ skey, int n, uint32_t invalid_key, uint32_t* ticket,
-            uint32_t* state, uint32_t* __restrict__ uidx, uint32_t* __restrict__ seg_start,
-            int64_t* __restrict__ out_rows, PlanHeader* hdr, int64_t* n_unique_out,
-            int num_tiles) {
+// Run-length heads of the sorted keys, in two launches with the kernel boundary as the only
+// synchronisation: k_head_count leaves every tile's head count in counts[], k_head_write sums
+// the counts of the tiles before its own (a coalesced read of <= tiles words; tiles <= a few
+// thousand for the batches of BASELINE.json) and writes uidx / seg_start / unique rows / U.
+__device__ __forceinline__ uint32_t tile_heads(const uint32_t* __restrict__ skey, int n,
+                                               uint32_t invalid_key, int idx0, uint32_t (&k)[kScanTile / 256],
+                                               uint32_t& headmask) {
   constexpr int kItems = kScanTile / 256;
-  __shared__ uint32_t s_warp_sum[8];
-  __shared__ uint32_t s_tile_excl;
-  __shared__ int s_tile;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) s_tile = static_cast<int>(atomicAdd(ticket, 1u));
-  __syncthreads();
-  const int tile = s_tile;
-  const int idx0 = tile * kScanTile + tid * kItems;
-  uint32_t k[kItems];
+  static_assert(kItems == 8, "two 16-byte loads per thread");
   uint32_t prev = (idx0 > 0 && idx0 - 1 < n) ? skey[idx0 - 1] : kNoKey;
+  if (idx0 + kItems <= n) {
+    const uint4 a = *reinterpret_cast<const uint4*>(skey + idx0);
+    const uint4 b = *reinterpret_cast<const uint4*>(skey + idx0 + 4);
+    k[0] = a.x; k[1] = a.y; k[2] = a.z; k[3] = a.w; k[4] = b.x; k[5] = b.y; k[6] = b.z; k[7] = b.w;
+  } else {
+#pragma unroll
+    for (int j = 0; j < kItems; ++j) k[j] = idx0 + j < n ? skey[idx0 + j] : kNoKey;
+  }
   uint32_t cnt = 0;
-  uint32_t headmask = 0;
+  headmask = 0;
 #pragma unroll
   for (int j = 0; j < kItems; ++j) {
-    const int idx = idx0 + j;
-    k[j] = idx < n ? skey[idx] : kNoKey;
-    const bool head = idx < n && k[j] != prev && k[j] != invalid_key;
+    const bool head = idx0 + j < n && k[j] != prev && k[j] != invalid_key;
     headmask |= head ? (1u << j) : 0u;
     cnt += head;
     prev = k[j];
   }
+  return cnt;
+}
+
+__global__ void __launch_bounds__(256)
+k_head_count(const uint32_t* __restrict__ skey, int n, uint32_t invalid_key,
+             uint32_t* __restrict__ counts) {
+  uint32_t k[kScanTile / 256], headmask;
+  const int idx0 = blockIdx.x * kScanTile + threadIdx.x * (kScanTile / 256);
+  const uint32_t cnt = tile_heads(skey, n, invalid_key, idx0, k, headmask);
+  const uint32_t w = __reduce_add_sync(0xffffffffu, cnt);
+  __shared__ uint32_t s_w[8];
+  if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = w;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += s_w[i];
+    counts[blockIdx.x] = t;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_head_write(const uint32_t* __restrict__ skey, int n, uint32_t invalid_key,
+             const uint32_t* __restrict__ counts, uint32_t* __restrict__ uidx,
+             uint32_t* __restrict__ seg_start, int64_t* __restrict__ out_rows, PlanHeader* hdr,
+             int64_t* n_unique_out) {
+  constexpr int kItems = kScanTile / 256;
+  __shared__ uint32_t s_warp_sum[8], s_warp_pre[8];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tile = blockIdx.x;
+  uint32_t before = 0;                       // heads in earlier tiles
+  for (int t = tid; t < tile; t += 256) before += counts[t];
+  uint32_t k[kItems], headmask;
+  const int idx0 = tile * kScanTile + tid * kItems;
+  const uint32_t cnt = tile_heads(skey, n, invalid_key, idx0, k, headmask);
   uint32_t incl = cnt;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
     const uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
     if (lane >= o) incl += up;
   }
+  before = __reduce_add_sync(0xffffffffu, before);
   if (lane == 31) s_warp_sum[warp] = incl;
+  if (lane == 0) s_warp_pre[warp] = before;
   __syncthreads();
-  uint32_t warp_off = 0, block_total = 0;
+  uint32_t warp_off = 0, block_total = 0, tile_excl = 0;
 #pragma unroll
   for (int w = 0; w < 8; ++w) {
     warp_off += (w < warp) ? s_warp_sum[w] : 0u;
     block_total += s_warp_sum[w];
+    tile_excl += s_warp_pre[w];
   }
-  if (tid == 0) {
-    uint32_t excl = 0;
-    if (tile == 0) {
-      st_relaxed(state, kFlagIncl | block_total);
-    } else {
-      st_relaxed(state + tile, kFlagAgg | block_total);
-      excl = look_back(state, tile, 1);
-      st_relaxed(state + tile, kFlagIncl | (excl + block_total));
-    }
-    s_tile_excl = excl;
-    if (tile == num_tiles - 1) {
-      hdr->n_unique = excl + block_total;
-      if (n_unique_out) *n_unique_out = static_cast<int64_t>(excl + block_total);
-    }
+  if (tid == 0 && tile == static_cast<int>(gridDim.x) - 1) {
+    hdr->n_unique = tile_excl + block_total;
+    if (n_unique_out) *n_unique_out = static_cast<int64_t>(tile_excl + block_total);
   }
-  __syncthreads();
-  uint32_t run = s_tile_excl + warp_off + incl - cnt;  // heads before this thread's items
+  uint32_t run = tile_excl + warp_off + incl - cnt;  // heads before this thread's items
+  uint32_t u[kItems];
 #pragma unroll
   for (int j = 0; j < kItems; ++j) {
-    const int idx = idx0 + j;
-    if (idx < n) {
-      const bool head = (headmask >> j) & 1u;
-      run += head;
-      const uint32_t u = run - 1u;  // (wraps for leading invalid-only data; never used)
-      uidx[idx] = u;
-      if (head) {
-        seg_start[u] = static_cast<uint32_t>(idx);
-        if (out_rows) out_rows[u] = static_cast<int64_t>(k[j]);
-      }
+    const bool head = (headmask >> j) & 1u;
+    run += head;
+    u[j] = run - 1u;  // (wraps for leading invalid-only data; never used)
+    if (head && idx0 + j < n) {
+      seg_start[u[j]] = static_cast<uint32_t>(idx0 + j);
+      if (out_rows) out_rows[u[j]] = static_cast<int64_t>(k[j]);
     }
+  }
+  if (idx0 + kItems <= n) {
+    *reinterpret_cast<uint4*>(uidx + idx0) = make_uint4(u[0], u[1], u[2], u[3]);
+    *reinterpret_cast<uint4*>(uidx + idx0 + 4) = make_uint4(u[4], u[5], u[6], u[7]);
+  } else {
+#pragma unroll
+    for (int j = 0; j < kItems; ++j)
+      if (idx0 + j < n) uidx[idx0 + j] = u[j];
   }
 }
 
@@ -584,7 +686,7 @@ Workspace make_workspace(int64_t n, int64_t d, int64_t elem_size) {
   auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes); return o; };
   L.off_hist = take(sizeof(uint32_t) * 4 * (1 << kDirectMaxBits));
   L.off_tickets = take(sizeof(uint32_t) * 8);
-  L.off_lookback = take(sizeof(uint32_t) * L.sort_tiles * lookback_words_per_tile(n));
+  L.off_lookback = take(sizeof(uint32_t) * (L.sort_tiles + 1) * lookback_words_per_tile(n));
   L.off_scan_state = take(sizeof(uint32_t) * L.scan_tiles);
   L.zero_bytes = off;
   L.off_plan = take(sizeof(PlanHeader));
@@ -655,7 +757,7 @@ cudaError_t launch_passes(const int64_t* rows, int n, uint32_t height, KeyMap km
 }  // namespace
 
 namespace {
-template <int BITS>
+template <int BITS, bool SCANNED>
 cudaError_t launch_passes_direct(const int64_t* rows, int n, uint32_t height, KeyMap km, int passes,
                                  char* ws, const Workspace& L, int32_t* status, cudaStream_t s) {
   constexpr int kBins = 1 << BITS;
@@ -665,15 +767,18 @@ cudaError_t launch_passes_direct(const int64_t* rows, int n, uint32_t height, Ke
                        reinterpret_cast<uint32_t*>(ws + L.off_perm[1])};
   uint32_t* hmat = reinterpret_cast<uint32_t*>(ws + L.off_lookback);
   const int tiles = static_cast<int>(L.sort_tiles);
-  const size_t per_pass = static_cast<size_t>(tiles) * kBins;
-  k_prepare_direct<BITS><<<tiles, kSortThreads, 0, s>>>(rows, n, height, km, passes, keys[0], hmat, status);
+  const size_t per_pass = static_cast<size_t>(tiles + 1) * kBins;   // + the totals row
+  k_prepare_direct<BITS><<<tiles, kSortThreads, 0, s>>>(rows, n, height, km, passes, keys[0], hmat,
+                                                        per_pass, status);
   for (int p = 0; p < passes; ++p) {
     uint32_t* hn = p + 1 < passes ? hmat + (p + 1) * per_pass : nullptr;
+    if constexpr (SCANNED)
+      k_colscan<<<kBins / kColscanBins, kColscanThreads, 0, s>>>(hmat + p * per_pass, tiles, kBins);
     if (p == 0)
-      k_radix_pass_direct<BITS, false><<<tiles, kSortThreads, 0, s>>>(
+      k_radix_pass_direct<BITS, false, SCANNED><<<tiles, kSortThreads, 0, s>>>(
           keys[0], nullptr, keys[1], perm[1], n, 0, hmat, hn);
     else
-      k_radix_pass_direct<BITS, true><<<tiles, kSortThreads, 0, s>>>(
+      k_radix_pass_direct<BITS, true, SCANNED><<<tiles, kSortThreads, 0, s>>>(
           keys[p & 1], perm[p & 1], keys[(p + 1) & 1], perm[(p + 1) & 1], n, p * BITS,
           hmat + p * per_pass, hn);
   }
@@ -709,18 +814,13 @@ cudaError_t launch_plan(const int64_t* rows, int64_t n, int64_t height, char* ws
   cudaError_t e;
   if (dp.direct) {
     switch (dp.bits) {
-      case 8: e = launch_passes_direct<8>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
-      case 9: e = launch_passes_direct<9>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
-      default: e = launch_passes_direct<10>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
+      case 8: e = launch_passes_direct<8, false>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
+      case 9: e = launch_passes_direct<9, false>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
+      default: e = launch_passes_direct<10, false>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
     }
   } else {
-    // only the words this plan uses need clearing
-    const size_t zero = L.off_lookback + sizeof(uint32_t) * static_cast<size_t>(dp.passes) *
-                                             L.sort_tiles * (1u << dp.bits);
-    e = cudaMemsetAsync(ws, 0, std::min(zero, L.zero_bytes), s);
-    if (e != cudaSuccess) return e;
-    e = dp.bits == 9 ? launch_passes<9>(rows, ni, h, km, dp.passes, ws, L, status, s)
-                     : launch_passes<8>(rows, ni, h, km, dp.passes, ws, L, status, s);
+    e = dp.bits == 9 ? launch_passes_direct<9, true>(rows, ni, h, km, dp.passes, ws, L, status, s)
+                     : launch_passes_direct<8, true>(rows, ni, h, km, dp.passes, ws, L, status, s);
   }
   if (e != cudaSuccess) return e;
   if (out) *out = plan_view(n, height, ws, L);
@@ -730,18 +830,13 @@ cudaError_t launch_plan(const int64_t* rows, int64_t n, int64_t height, char* ws
 cudaError_t launch_head_scan(const SortedPlan& plan, int64_t n, uint32_t invalid_key, char* ws,
                              const Workspace& L, int64_t* out_rows, int64_t* n_unique_out,
                              cudaStream_t s) {
-  uint32_t* tickets = reinterpret_cast<uint32_t*>(ws + L.off_tickets);
-  uint32_t* state = reinterpret_cast<uint32_t*>(ws + L.off_scan_state);
-  // the scan may run more than once per plan (merge_add after plan_rows): reset its state
-  cudaError_t e = cudaMemsetAsync(state, 0, sizeof(uint32_t) * L.scan_tiles, s);
-  if (e != cudaSuccess) return e;
-  e = cudaMemsetAsync(tickets + kMaxPasses, 0, sizeof(uint32_t), s);
-  if (e != cudaSuccess) return e;
-  k_head_scan<<<static_cast<int>(L.scan_tiles), 256, 0, s>>>(
-      plan.keys, static_cast<int>(n), invalid_key, tickets + kMaxPasses, state,
+  uint32_t* counts = reinterpret_cast<uint32_t*>(ws + L.off_scan_state);
+  const int tiles = static_cast<int>(L.scan_tiles);
+  k_head_count<<<tiles, 256, 0, s>>>(plan.keys, static_cast<int>(n), invalid_key, counts);
+  k_head_write<<<tiles, 256, 0, s>>>(
+      plan.keys, static_cast<int>(n), invalid_key, counts,
       reinterpret_cast<uint32_t*>(ws + L.off_uidx), reinterpret_cast<uint32_t*>(ws + L.off_seg_start),
-      out_rows, reinterpret_cast<PlanHeader*>(ws + L.off_plan), n_unique_out,
-      static_cast<int>(L.scan_tiles));
+      out_rows, reinterpret_cast<PlanHeader*>(ws + L.off_plan), n_unique_out);
   return cudaGetLastError();
 }
 

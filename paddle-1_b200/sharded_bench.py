@@ -126,8 +126,9 @@ def run(args):
         b_own = recv_rows * (8 + 2 * 4 * d) + recv_rows * (8 + 4 * d) + recv_rows * 2 * 4 * d
         hbm = (b_req + b_own) / (ms_per_step * 1e-3) / 1e9
         nv = float(sent.item()) / args.steps / (ms_per_step * 1e-3) / 1e9
-        passes = capi.radix_passes(n, tab.plan_h)
-        launches = (1 + passes) + 1 + 1 + 1 + 1 + 3 + (1 + capi.radix_passes(recv_rows, tab.hs)) + 2
+        hs = capi.HEAD_SCAN_KERNELS
+        launches = (capi.plan_kernel_count(n, tab.plan_h) + hs) + 1 + 1 + 1 + 1 + 3 + \
+                   (capi.plan_kernel_count(recv_rows, tab.hs) + hs) + 2
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,

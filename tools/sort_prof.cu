@@ -2,6 +2,8 @@
 //   nvcc -O3 -std=c++20 -gencode arch=compute_100a,code=sm_100a -DB200EMB_PROFILE -o tools/sort_prof tools/sort_prof.cu
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
+#include <numeric>
 #include <vector>
 #include "../paddle-1_b200/csrc/sort.cu"
 namespace b200emb {
@@ -28,6 +30,27 @@ int main(int argc, char** argv) {
   cudaEventRecord(e1); cudaDeviceSynchronize();
   float ms; cudaEventElapsedTime(&ms, e0, e1);
   printf("n=%d passes=%d  %.2f us per plan (%s)\n", n, plan.passes, ms / 20 * 1e3, cudaGetErrorString(cudaGetLastError()));
+  cudaEventRecord(e0);
+  for (int it = 0; it < 20; ++it)
+    launch_head_scan(plan, n, static_cast<uint32_t>(height), ws, L, nullptr, nullptr, 0);
+  cudaEventRecord(e1); cudaDeviceSynchronize();
+  cudaEventElapsedTime(&ms, e0, e1);
+  printf("head scan %.2f us (%s)\n", ms / 20 * 1e3, cudaGetErrorString(cudaGetLastError()));
+  {  // check against a host stable sort
+    std::vector<uint32_t> k(n), pm(n), ui(n), want(n);
+    cudaMemcpy(k.data(), plan.keys, n * 4, cudaMemcpyDeviceToHost);
+    cudaMemcpy(pm.data(), plan.perm, n * 4, cudaMemcpyDeviceToHost);
+    cudaMemcpy(ui.data(), ws + L.off_uidx, n * 4, cudaMemcpyDeviceToHost);
+    std::iota(want.begin(), want.end(), 0u);
+    std::stable_sort(want.begin(), want.end(), [&](uint32_t a, uint32_t b) { return h[a] < h[b]; });
+    long bad = 0; uint32_t u = 0;
+    for (int i = 0; i < n; ++i) {
+      if (i > 0 && h[want[i]] != h[want[i - 1]]) ++u;
+      bad += pm[i] != want[i] || k[i] != static_cast<uint32_t>(h[want[i]]) || ui[i] != u;
+    }
+    PlanHeader hd; cudaMemcpy(&hd, ws + L.off_plan, sizeof(hd), cudaMemcpyDeviceToHost);
+    printf("check: %ld mismatches, U=%u (want %u)\n", bad, (unsigned)hd.n_unique, u + 1);
+  }
   static long long prof[256][8];
   cudaMemcpyFromSymbol(prof, g_sort_prof, sizeof(prof));
   const int tiles = (int)L.sort_tiles;
