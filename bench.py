@@ -221,8 +221,8 @@ def run_single(args):
         capi.sparse_sgd(table, ids[b], dout[b], lr, ws[b], capi.PLAN_READY, status)
         main.wait_stream(side)
 
-    # gather, sort plan, head scan, chunk reduce, fixup
-    kernels_per_step = 1 + capi.plan_kernel_count(n, v) + capi.HEAD_SCAN_KERNELS + 2
+    # gather, sort plan, chunk reduce, fixup (fast-mode SGD finds the run heads itself: no head scan)
+    kernels_per_step = 1 + capi.plan_kernel_count(n, v) + 2
 
     graphs = []
     with torch.cuda.stream(main):

@@ -99,7 +99,8 @@ int b200emb_plan_rows(const int64_t* rows, int64_t n, int64_t height, void* work
  * (operators/split_ids_op.h:36-58, `PADDLE_THROW` on GPU at :30-32): owner(id) = id % num_shards,
  * local row = id / num_shards.  Sorts rows by key = owner * ceil(height/num_shards) + local row and
  * de-duplicates them:
- *   unique_keys[0..U)  ascending unique keys (must hold n entries), *n_unique = U (device int64),
+ *   unique_keys[0..U)  (nullable unless one of the three outputs below is wanted) ascending unique
+ *                      keys (must hold n entries), *n_unique = U (nullable device int64),
  *   shard_bounds[g]    (nullable, num_shards+1 entries) first unique index owned by shard g,
  *   elem_bounds[g]     (nullable, num_shards+1 entries) first position, in plan order, owned by shard g,
  *   local_rows[0..U)   (nullable) key % shard_height = the row inside the owner's shard.

@@ -90,12 +90,11 @@ def _need_cuda(*tensors):
 
 
 def radix_passes(n, height):
-    """Radix passes of the sort plan (sort.cu digit_plan): <=10-bit digits up to 64 tiles of 2048, else <=9-bit."""
+    """Radix passes of the sort plan (sort.cu digit_plan): digits of up to 10 bits."""
     bits = 1
     while (1 << bits) <= int(height):
         bits += 1
-    maxb = 10 if (n + 2047) // 2048 <= 64 else 9
-    return (bits + maxb - 1) // maxb
+    return (bits + 9) // 10
 
 
 HEAD_SCAN_KERNELS = 2   # k_head_count + k_head_write
@@ -121,9 +120,8 @@ def alloc_workspace(n, d, elem_size=4, device="cuda"):
 
 
 def alloc_workspace_upto(n_max, d, elem_size=4, device="cuda"):
-    """Workspace valid for ANY n <= n_max (the layout switches sort modes at 131 072 ids, so the
-    requirement is not monotonic across that boundary)."""
-    nbytes = max(workspace_bytes(n_max, d, elem_size), workspace_bytes(min(n_max, 131072), d, elem_size), 256)
+    """Workspace valid for ANY n <= n_max (the requirement grows monotonically with n)."""
+    nbytes = max(workspace_bytes(n_max, d, elem_size), 256)
     return torch.empty(nbytes, dtype=torch.uint8, device=device)
 
 
@@ -180,8 +178,16 @@ def sum_selected_rows(inputs):
     return out_rows, out_value
 
 
-def plan_rows(rows, height, workspace, status=None):
+def plan_rows(rows, height, workspace, status=None, unique=False):
+    """Sort plan of `rows` into the workspace.  unique=True also leaves the unique index there
+    (plan_unique_rows with one shard and no outputs): consumers then take PLAN_READY | UNIQUE_READY."""
     _need_cuda(rows, workspace, status)
+    if unique:
+        _check(lib().b200emb_plan_unique_rows(
+            _ptr(rows), ctypes.c_int64(rows.numel()), ctypes.c_int64(height), ctypes.c_int64(1), None, None,
+            None, None, None, _ptr(workspace), ctypes.c_size_t(workspace.numel()), _ptr(status), _stream()),
+            "plan_unique_rows")
+        return
     _check(lib().b200emb_plan_rows(_ptr(rows), ctypes.c_int64(rows.numel()), ctypes.c_int64(height),
                                    _ptr(workspace), ctypes.c_size_t(workspace.numel()), _ptr(status),
                                    _stream()), "plan_rows")

@@ -170,9 +170,9 @@ int b200emb_plan_unique_rows(const int64_t* rows, int64_t n, int64_t height, int
   const int64_t plan_height = num_shards > 1 ? num_shards * shard_height : height;
   if (plan_height >= 0xFFFFFFFFLL) return B200EMB_E_UNSUPPORTED;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (!n_unique || (n > 0 && (!rows || !unique_keys))) return B200EMB_E_INVALID;
+  if (n > 0 && !rows) return B200EMB_E_INVALID;
   if (n == 0) {
-    cudaError_t e = cudaMemsetAsync(n_unique, 0, sizeof(int64_t), s);
+    cudaError_t e = n_unique ? cudaMemsetAsync(n_unique, 0, sizeof(int64_t), s) : cudaSuccess;
     if (e == cudaSuccess && shard_bounds)
       e = cudaMemsetAsync(shard_bounds, 0, sizeof(int64_t) * (num_shards + 1), s);
     if (e == cudaSuccess && elem_bounds)
@@ -193,6 +193,7 @@ int b200emb_plan_unique_rows(const int64_t* rows, int64_t n, int64_t height, int
   e = launch_head_scan(plan, n, static_cast<uint32_t>(plan_height), ws, L, unique_keys, n_unique, s);
   if (e != cudaSuccess) return fail_cuda(e);
   if (shard_bounds || elem_bounds || local_rows) {
+    if (!unique_keys) return B200EMB_E_INVALID;   // the split reads the unique keys
     e = launch_shard_split(unique_keys, plan, ws, L, static_cast<int>(num_shards),
                            static_cast<uint32_t>(num_shards > 1 ? shard_height : plan_height), n,
                            static_cast<uint32_t>(plan_height), shard_bounds, elem_bounds, local_rows, s);

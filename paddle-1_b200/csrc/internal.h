@@ -25,12 +25,9 @@ inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 
 // Everything the kernels keep in the caller's workspace.  Offsets in bytes.
 struct Workspace {
-  // zeroed at the start of every plan
-  size_t off_hist;        // u32 [passes][bins]         global digit histograms (<= 3 x 4096)
-  size_t off_tickets;     // u32 [8]                    dynamic tile counters (4 sort passes, 1 scan)
-  size_t off_lookback;    // u32 [passes][sort_tiles][bins]
-  size_t off_scan_state;  // u32 [scan_tiles]
-  size_t zero_bytes;      // bytes [0, zero_bytes) are cleared by cudaMemsetAsync
+  // sort scratch (nothing here needs clearing between plans)
+  size_t off_digit_counts;  // u32 [passes][sort_tiles + 1][bins]  per-tile digit counts / prefixes
+  size_t off_scan_state;    // u32 [scan_tiles]                    head counts per scan tile
   // plan
   size_t off_plan;        // PlanHeader
   size_t off_keys[2];     // u32 [n]

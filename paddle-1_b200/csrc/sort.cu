@@ -3,17 +3,21 @@
 // Replaces the host-side std::set + per-row linear scan of the reference's MergeAdd
 // (operators/math/selected_rows_functor.cc:193-228, .cu:235-297) with a stable LSD radix
 // sort of (id -> original position) done entirely on the device:
-//   k_prepare      int64 ids -> u32 keys (+ range check) and the global digit histograms of
-//                  every pass in one sweep;
-//   k_radix_pass   one launch per 8-bit digit: warp-level match ranking (stable), tile
-//                  aggregates published to a chained-scan state array, batched decoupled
-//                  look-back, scatter;
-//   k_head_scan    run-length heads of the sorted keys -> unique index of every element,
-//                  first position of every unique row, ascending unique rows (= std::set
-//                  order), U.
-// Only ceil(log2(height+1)) key bits are sorted.  The sort moves 8 B per id per pass, which is
-// noise next to the 4*D B of row data each id drags through HBM; launch count and look-back
-// latency are what matter, hence the 1+passes launch structure.
+//   k_prepare_direct   int64 ids -> u32 keys (+ range check) and the first pass's per-tile digit
+//                      counts H[0][tile][bin]; clears the later passes' matrices;
+//   k_colscan          (above 64 tiles) turns H[pass] into exclusive prefixes over tiles;
+//   k_radix_pass_direct  one launch per digit of up to 10 bits: warp-level match ranking
+//                      (stable), scatter, and — while scattering — the NEXT pass's H counted with
+//                      integer reductions keyed by (destination tile, next digit);
+//   k_head_count / k_head_write   run-length heads of the sorted keys -> unique index of every
+//                      element, first position of every unique row, ascending unique rows
+//                      (= std::set order), U.
+// Only ceil(log2(height+1)) key bits are sorted.  The kernel boundary is the only
+// synchronisation: no flags, no polling, no look-back, no memset (an earlier chained-scan
+// version lost 12-17k cycles per tile to look-back waits at 832 tiles; profiles/r1_notes.md).
+// The sort moves 8 B per id per pass, which is noise next to the 4*D B of row data each id
+// drags through HBM; launch count is what matters for small batches, scatter throughput
+// (~40 G key-passes/s) for large ones.
 #include <algorithm>
 #include <cstdlib>
 
@@ -23,68 +27,6 @@
 namespace b200emb {
 
 namespace {
-#ifdef B200EMB_PROFILE
-__device__ long long g_sort_prof[256][8];
-#define SORT_STAMP(i) do { if (threadIdx.x == 0 && tile < 256) g_sort_prof[tile][i] = clock64(); } while (0)
-#else
-#define SORT_STAMP(i) do { } while (0)
-#endif
-constexpr uint32_t kFlagAgg = 1u << 30;
-constexpr uint32_t kFlagIncl = 2u << 30;
-constexpr uint32_t kValMask = (1u << 30) - 1;
-
-// Walk back over predecessor tiles' published words (one counter per tile, `stride` words
-// apart) until an inclusive prefix is met.  Loads are issued kLookBatch at a time so the walk
-// costs one L2 round trip per batch rather than per tile.
-template <int kLookBatch = 16>
-__device__ __forceinline__ uint32_t look_back(const uint32_t* state, int tile, size_t stride) {
-  uint32_t excl = 0;
-  int t = tile - 1;
-  while (t >= 0) {
-    uint32_t v[kLookBatch];
-#pragma unroll
-    for (int i = 0; i < kLookBatch; ++i) {
-      const int tt = t - i;
-      v[i] = tt >= 0 ? ld_relaxed(state + static_cast<size_t>(tt) * stride) : kFlagIncl;
-    }
-    int adv = 0;
-    bool fin = false, stall = false;
-#pragma unroll
-    for (int i = 0; i < kLookBatch; ++i) {
-      if (!fin && !stall) {
-        const uint32_t f = v[i] >> 30;
-        if (f == 0) {
-          stall = true;
-        } else {
-          excl += v[i] & kValMask;
-          ++adv;
-          fin = (f == 2);
-        }
-      }
-    }
-    if (fin) break;
-    t -= adv;
-  }
-  return excl;
-}
-
-// K consecutive counters per tile (one thread's bins), fetched with 16-byte loads, LB tiles in
-// flight per round trip.  Each 32-bit word carries its own flag, so torn vectors are harmless.
-template <int K>
-__device__ __forceinline__ void ld_state_vec(const uint32_t* p, uint32_t (&v)[K]) {
-  if constexpr (K == 1) {
-    v[0] = ld_relaxed(p);
-  } else if constexpr (K == 2) {
-    asm volatile("ld.volatile.global.v2.u32 {%0,%1}, [%2];" : "=r"(v[0]), "=r"(v[1]) : "l"(p) : "memory");
-  } else {
-#pragma unroll
-    for (int q = 0; q < K / 4; ++q)
-      asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
-                   : "=r"(v[4 * q]), "=r"(v[4 * q + 1]), "=r"(v[4 * q + 2]), "=r"(v[4 * q + 3])
-                   : "l"(p + 4 * q) : "memory");
-  }
-}
-
 // plain (non-polling) vector load of K counters, L2-cached only
 template <int K>
 __device__ __forceinline__ void ld_cg_vec(const uint32_t* p, uint32_t (&v)[K]) {
@@ -100,209 +42,6 @@ __device__ __forceinline__ void ld_cg_vec(const uint32_t* p, uint32_t (&v)[K]) {
       v[4 * q] = t.x; v[4 * q + 1] = t.y; v[4 * q + 2] = t.z; v[4 * q + 3] = t.w;
     }
   }
-}
-
-template <int K, int LB>
-__device__ __forceinline__ void look_back_vec(const uint32_t* state, int tile, size_t stride,
-                                              uint32_t (&excl)[K]) {
-  bool fin[K];
-#pragma unroll
-  for (int k = 0; k < K; ++k) fin[k] = false;
-  int t = tile - 1;
-  while (t >= 0) {
-    uint32_t v[LB][K];
-#pragma unroll
-    for (int i = 0; i < LB; ++i) {
-      const int tt = t - i;
-      if (tt >= 0) {
-        ld_state_vec<K>(state + static_cast<size_t>(tt) * stride, v[i]);
-      } else {
-#pragma unroll
-        for (int k = 0; k < K; ++k) v[i][k] = kFlagIncl;
-      }
-    }
-    int adv = 0;
-    bool stall = false, all_fin = false;
-#pragma unroll
-    for (int i = 0; i < LB; ++i) {
-      if (!stall && !all_fin) {
-        bool ready = true;
-#pragma unroll
-        for (int k = 0; k < K; ++k) ready = ready && (fin[k] || (v[i][k] >> 30) != 0);
-        if (!ready) {
-          stall = true;
-        } else {
-          all_fin = true;
-#pragma unroll
-          for (int k = 0; k < K; ++k) {
-            if (!fin[k]) {
-              excl[k] += v[i][k] & kValMask;
-              fin[k] = (v[i][k] >> 30) == 2;
-            }
-            all_fin = all_fin && fin[k];
-          }
-          ++adv;
-        }
-      }
-    }
-    if (all_fin) break;
-    t -= adv;
-  }
-}
-
-// Digit width is a template parameter: 8 bits for large N (small look-back state), up to 12 bits
-// for small N where every pass saved is a launch + chained scan saved.
-template <int BITS>
-__global__ void __launch_bounds__(256)
-k_prepare(const int64_t* __restrict__ rows, int n, uint32_t height, KeyMap km, int passes,
-          uint32_t* __restrict__ keys, uint32_t* __restrict__ ghist, int32_t* status) {
-  constexpr int kBins = 1 << BITS;
-  extern __shared__ uint32_t sh[];   // [passes][kBins]
-  const int tid = threadIdx.x, lane = tid & 31;
-  for (int i = tid; i < passes * kBins; i += blockDim.x) sh[i] = 0;
-  __syncthreads();
-  bool bad = false;
-  const int stride = gridDim.x * blockDim.x;
-  for (int base = blockIdx.x * blockDim.x; base < n; base += stride) {
-    const int i = base + tid;
-    const bool valid = i < n;
-    uint32_t key = 0;
-    if (valid) {
-      const int64_t r = rows[i];
-      const bool ok = r >= 0 && r < static_cast<int64_t>(km.raw_height);
-      key = ok ? km(static_cast<uint32_t>(r)) : height;  // out-of-range rows sort last
-      bad |= !ok;
-      keys[i] = key;
-    }
-    for (int p = 0; p < passes; ++p) {
-      const uint32_t digit = (key >> (p * BITS)) & (kBins - 1);
-      const uint32_t peers = match_digit<BITS>(digit, valid);
-      if (valid && lane == __ffs(peers) - 1) atomicAdd(&sh[p * kBins + digit], __popc(peers));
-    }
-  }
-  __syncthreads();
-  for (int i = tid; i < passes * kBins; i += blockDim.x)
-    if (sh[i]) atomicAdd(&ghist[i], sh[i]);
-  if (bad && status) atomicOr(status, 2);
-}
-
-template <int BITS, bool HAS_PERM_IN>
-__global__ void __launch_bounds__(kSortThreads)
-k_radix_pass(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ perm_in,
-             uint32_t* __restrict__ keys_out, uint32_t* __restrict__ perm_out, int n, int shift,
-             const uint32_t* __restrict__ ghist, uint32_t* ticket, uint32_t* state) {
-  constexpr int kWarps = kSortThreads / 32;
-  constexpr int kBins = 1 << BITS;
-  constexpr int K = kBins / kSortThreads;          // bins owned by one thread (consecutive)
-  constexpr int kLb = K >= 8 ? 4 : (K == 4 ? 12 : 16);  // predecessor tiles in flight
-  extern __shared__ __align__(16) unsigned char sort_smem[];
-  uint32_t* s_base = reinterpret_cast<uint32_t*>(sort_smem);            // [kBins]
-  uint16_t* s_cnt = reinterpret_cast<uint16_t*>(s_base + kBins);        // [kWarps][kBins]
-  __shared__ uint32_t s_warp_sum[kWarps];
-  __shared__ int s_tile;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) s_tile = static_cast<int>(atomicAdd(ticket, 1u));
-  {
-    uint32_t* z = reinterpret_cast<uint32_t*>(s_cnt);
-    for (int i = tid; i < kWarps * kBins / 2; i += kSortThreads) z[i] = 0;
-  }
-  __syncthreads();
-  const int tile = s_tile;
-  const int warp_start = tile * kSortTile + warp * (32 * kSortItems);
-  uint16_t* my_cnt = s_cnt + warp * kBins;
-  SORT_STAMP(0);
-
-  uint32_t key[kSortItems], pm[kSortItems], rank[kSortItems];
-#pragma unroll
-  for (int j = 0; j < kSortItems; ++j) {
-    const int idx = warp_start + j * 32 + lane;
-    const bool valid = idx < n;
-    key[j] = valid ? keys_in[idx] : 0u;
-    pm[j] = valid ? (HAS_PERM_IN ? perm_in[idx] : static_cast<uint32_t>(idx)) : 0u;
-  }
-  // stable rank inside the warp: items are ordered (j, lane) == ascending idx
-  const uint32_t lt = lanemask_lt();
-  SORT_STAMP(1);
-#pragma unroll
-  for (int j = 0; j < kSortItems; ++j) {
-    const bool valid = (warp_start + j * 32 + lane) < n;
-    const uint32_t digit = (key[j] >> shift) & (kBins - 1);
-    const uint32_t peers = match_digit<BITS>(digit, valid);
-    const int leader = valid ? __ffs(peers) - 1 : lane;
-    uint32_t old = 0;
-    if (valid && lane == leader) {
-      old = my_cnt[digit];
-      my_cnt[digit] = static_cast<uint16_t>(old + __popc(peers));
-    }
-    old = __shfl_sync(0xffffffffu, old, leader);
-    rank[j] = old + __popc(peers & lt);
-    __syncwarp();
-  }
-  __syncthreads();
-  SORT_STAMP(2);
-  // bins tid*K .. tid*K+K-1: exclusive offsets of each warp inside the tile, tile totals
-  uint32_t total[K], excl[K];
-#pragma unroll
-  for (int k = 0; k < K; ++k) {
-    const int bin = tid * K + k;
-    uint32_t t = 0;
-#pragma unroll
-    for (int w = 0; w < kWarps; ++w) {
-      const uint32_t c = s_cnt[w * kBins + bin];
-      s_cnt[w * kBins + bin] = static_cast<uint16_t>(t);
-      t += c;
-    }
-    total[k] = t;
-    excl[k] = 0;
-  }
-  uint32_t* my_state = state + static_cast<size_t>(tile) * kBins + tid * K;
-  uint32_t g[K], gsum = 0;   // global histogram of this thread's bins (fetched ahead of the look-back)
-#pragma unroll
-  for (int k = 0; k < K; ++k) g[k] = ghist[tid * K + k];
-  SORT_STAMP(3);
-  if (tile == 0) {
-#pragma unroll
-    for (int k = 0; k < K; ++k) st_relaxed(my_state + k, kFlagIncl | total[k]);
-  } else {
-#pragma unroll
-    for (int k = 0; k < K; ++k) st_relaxed(my_state + k, kFlagAgg | total[k]);
-    look_back_vec<K, kLb>(state + tid * K, tile, kBins, excl);
-#pragma unroll
-    for (int k = 0; k < K; ++k) st_relaxed(my_state + k, kFlagIncl | (excl[k] + total[k]));
-  }
-  SORT_STAMP(4);
-  // exclusive scan of the global histogram over bins (thread-local K, then warp, then block)
-#pragma unroll
-  for (int k = 0; k < K; ++k) gsum += g[k];
-  uint32_t incl = gsum;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
-    if (lane >= o) incl += up;
-  }
-  if (lane == 31) s_warp_sum[warp] = incl;
-  __syncthreads();
-  uint32_t run = incl - gsum;
-#pragma unroll
-  for (int w = 0; w < kWarps; ++w) run += (w < warp) ? s_warp_sum[w] : 0u;
-#pragma unroll
-  for (int k = 0; k < K; ++k) {
-    s_base[tid * K + k] = run + excl[k];
-    run += g[k];
-  }
-  __syncthreads();
-  SORT_STAMP(5);
-#pragma unroll
-  for (int j = 0; j < kSortItems; ++j) {
-    const int idx = warp_start + j * 32 + lane;
-    if (idx < n) {
-      const uint32_t digit = (key[j] >> shift) & (kBins - 1);
-      const uint32_t pos = s_base[digit] + my_cnt[digit] + rank[j];
-      keys_out[pos] = key[j];
-      perm_out[pos] = pm[j];
-    }
-  }
-  SORT_STAMP(6);
 }
 
 // ---- small batches (<= kDirectMaxTiles tiles): no chained scan at all --------------------
@@ -653,26 +392,22 @@ int key_bits(int64_t height) {  // keys span [0, height] (height = the invalid s
   return b;
 }
 
-// Small batches are launch/latency bound: the direct-prefix mode spends shared memory on digits
-// of up to 10 bits to save passes.  Larger batches keep 8-bit digits (the chained scan's walk
-// costs one counter per bin per predecessor tile, so wide digits lose there).
-constexpr int kDirectMaxBits = 10;
-constexpr int kLookbackMaxBits = 9;   // 27-bit keys (100M-row tables) sort in 3 passes instead of 4
+// Digits of up to 10 bits (20 KB of shared counters per CTA) to save passes; the fewest passes
+// that cover the key, then the narrowest digit that still fits them.
+constexpr int kMaxDigitBits = 10;
 struct DigitPlan { int passes, bits; bool direct; };
 DigitPlan digit_plan(int64_t n, int64_t height) {
   const int kb = key_bits(height);
   DigitPlan p;
   p.direct = ceil_div(n, kSortTile) <= kDirectMaxTiles;
-  const int maxb = p.direct ? kDirectMaxBits : kLookbackMaxBits;
-  p.passes = static_cast<int>(ceil_div(kb, maxb));
+  p.passes = static_cast<int>(ceil_div(kb, kMaxDigitBits));
   p.bits = static_cast<int>(ceil_div(kb, p.passes));
   if (p.bits < kRadixBits) p.bits = kRadixBits;
   return p;
 }
-// counter words per tile the workspace must hold for any height at this n
-int64_t lookback_words_per_tile(int64_t n) {
-  return ceil_div(n, kSortTile) <= kDirectMaxTiles ? 4LL * (1 << kDirectMaxBits) : 4LL * (1 << kLookbackMaxBits);
-}
+// counter words per tile the workspace must hold for any height: passes x bins <= 3 x 1024
+constexpr int64_t kDigitWordsPerTile = 3LL * (1 << kMaxDigitBits);
+static_assert(kMaxPasses * (1 << kRadixBits) <= kDigitWordsPerTile, "4 passes of 8 bits");
 
 }  // namespace
 
@@ -684,11 +419,8 @@ Workspace make_workspace(int64_t n, int64_t d, int64_t elem_size) {
   L.max_ctas = ceil_div(n, static_cast<int64_t>(kMinGroupsPerCta) * kMinChunk) + 1;
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes); return o; };
-  L.off_hist = take(sizeof(uint32_t) * 4 * (1 << kDirectMaxBits));
-  L.off_tickets = take(sizeof(uint32_t) * 8);
-  L.off_lookback = take(sizeof(uint32_t) * (L.sort_tiles + 1) * lookback_words_per_tile(n));
+  L.off_digit_counts = take(sizeof(uint32_t) * (L.sort_tiles + 1) * kDigitWordsPerTile);
   L.off_scan_state = take(sizeof(uint32_t) * L.scan_tiles);
-  L.zero_bytes = off;
   L.off_plan = take(sizeof(PlanHeader));
   for (int b = 0; b < 2; ++b) L.off_keys[b] = take(sizeof(uint32_t) * n);
   for (int b = 0; b < 2; ++b) L.off_perm[b] = take(sizeof(uint32_t) * n);
@@ -712,51 +444,6 @@ SortedPlan plan_view(int64_t n, int64_t height, char* ws, const Workspace& L) {
 }
 
 namespace {
-template <int BITS>
-cudaError_t launch_passes(const int64_t* rows, int n, uint32_t height, KeyMap km, int passes,
-                          char* ws, const Workspace& L, int32_t* status, cudaStream_t s) {
-  constexpr int kBins = 1 << BITS;
-  uint32_t* keys[2] = {reinterpret_cast<uint32_t*>(ws + L.off_keys[0]),
-                       reinterpret_cast<uint32_t*>(ws + L.off_keys[1])};
-  uint32_t* perm[2] = {reinterpret_cast<uint32_t*>(ws + L.off_perm[0]),
-                       reinterpret_cast<uint32_t*>(ws + L.off_perm[1])};
-  uint32_t* ghist = reinterpret_cast<uint32_t*>(ws + L.off_hist);
-  uint32_t* tickets = reinterpret_cast<uint32_t*>(ws + L.off_tickets);
-  uint32_t* lookback = reinterpret_cast<uint32_t*>(ws + L.off_lookback);
-  const size_t prep_smem = sizeof(uint32_t) * passes * kBins;
-  const size_t pass_smem = sizeof(uint32_t) * kBins + sizeof(uint16_t) * (kSortThreads / 32) * kBins;
-  cudaError_t e;
-  if (prep_smem > 48 * 1024) {
-    e = cudaFuncSetAttribute(k_prepare<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             static_cast<int>(prep_smem));
-    if (e != cudaSuccess) return e;
-  }
-  if (pass_smem > 48 * 1024) {
-    e = cudaFuncSetAttribute(k_radix_pass<BITS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             static_cast<int>(pass_smem));
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(k_radix_pass<BITS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             static_cast<int>(pass_smem));
-    if (e != cudaSuccess) return e;
-  }
-  const int prep_grid = static_cast<int>(std::min<int64_t>(ceil_div(n, 256 * 4), 148 * 4));
-  k_prepare<BITS><<<prep_grid, 256, prep_smem, s>>>(rows, n, height, km, passes, keys[0], ghist, status);
-  const int tiles = static_cast<int>(L.sort_tiles);
-  for (int p = 0; p < passes; ++p) {
-    uint32_t* st = lookback + static_cast<size_t>(p) * L.sort_tiles * kBins;
-    if (p == 0)
-      k_radix_pass<BITS, false><<<tiles, kSortThreads, pass_smem, s>>>(
-          keys[0], nullptr, keys[1], perm[1], n, 0, ghist, tickets + p, st);
-    else
-      k_radix_pass<BITS, true><<<tiles, kSortThreads, pass_smem, s>>>(
-          keys[p & 1], perm[p & 1], keys[(p + 1) & 1], perm[(p + 1) & 1], n, p * BITS,
-          ghist + p * kBins, tickets + p, st);
-  }
-  return cudaGetLastError();
-}
-}  // namespace
-
-namespace {
 template <int BITS, bool SCANNED>
 cudaError_t launch_passes_direct(const int64_t* rows, int n, uint32_t height, KeyMap km, int passes,
                                  char* ws, const Workspace& L, int32_t* status, cudaStream_t s) {
@@ -765,7 +452,7 @@ cudaError_t launch_passes_direct(const int64_t* rows, int n, uint32_t height, Ke
                        reinterpret_cast<uint32_t*>(ws + L.off_keys[1])};
   uint32_t* perm[2] = {reinterpret_cast<uint32_t*>(ws + L.off_perm[0]),
                        reinterpret_cast<uint32_t*>(ws + L.off_perm[1])};
-  uint32_t* hmat = reinterpret_cast<uint32_t*>(ws + L.off_lookback);
+  uint32_t* hmat = reinterpret_cast<uint32_t*>(ws + L.off_digit_counts);
   const int tiles = static_cast<int>(L.sort_tiles);
   const size_t per_pass = static_cast<size_t>(tiles + 1) * kBins;   // + the totals row
   k_prepare_direct<BITS><<<tiles, kSortThreads, 0, s>>>(rows, n, height, km, passes, keys[0], hmat,
@@ -819,8 +506,11 @@ cudaError_t launch_plan(const int64_t* rows, int64_t n, int64_t height, char* ws
       default: e = launch_passes_direct<10, false>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
     }
   } else {
-    e = dp.bits == 9 ? launch_passes_direct<9, true>(rows, ni, h, km, dp.passes, ws, L, status, s)
-                     : launch_passes_direct<8, true>(rows, ni, h, km, dp.passes, ws, L, status, s);
+    switch (dp.bits) {
+      case 8: e = launch_passes_direct<8, true>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
+      case 9: e = launch_passes_direct<9, true>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
+      default: e = launch_passes_direct<10, true>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
+    }
   }
   if (e != cudaSuccess) return e;
   if (out) *out = plan_view(n, height, ws, L);

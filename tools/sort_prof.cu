@@ -1,4 +1,4 @@
-// Developer tool: per-phase cycle stamps of the multi-launch radix sort plan.
+// Developer tool: times the sort plan and the head scan alone and checks them against a host stable sort.
 //   nvcc -O3 -std=c++20 -gencode arch=compute_100a,code=sm_100a -DB200EMB_PROFILE -o tools/sort_prof tools/sort_prof.cu
 #include <cstdio>
 #include <cstdlib>
@@ -50,17 +50,6 @@ int main(int argc, char** argv) {
     }
     PlanHeader hd; cudaMemcpy(&hd, ws + L.off_plan, sizeof(hd), cudaMemcpyDeviceToHost);
     printf("check: %ld mismatches, U=%u (want %u)\n", bad, (unsigned)hd.n_unique, u + 1);
-  }
-  static long long prof[256][8];
-  cudaMemcpyFromSymbol(prof, g_sort_prof, sizeof(prof));
-  const int tiles = (int)L.sort_tiles;
-  long long t0 = prof[0][0];
-  for (int t = 0; t < tiles && t < 256; ++t) if (prof[t][0] < t0) t0 = prof[t][0];
-  const char* names[] = {"load", "rank", "warp-reduce", "lookback", "ghist scan", "scatter"};
-  for (int t = 0; t < tiles && t < 256; t += (tiles > 16 ? tiles / 8 : 1)) {
-    printf("tile %3d start +%6lld:", t, prof[t][0] - t0);
-    for (int k = 0; k < 6; ++k) printf(" %s %lld", names[k], prof[t][k + 1] - prof[t][k]);
-    printf("  end +%lld\n", prof[t][6] - t0);
   }
   return 0;
 }
