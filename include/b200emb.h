@@ -144,6 +144,42 @@ int b200emb_merge_ids_f32(const float* x, int64_t n, int64_t d, int64_t shard_nu
 int b200emb_merge_ids_f64(const double* x, int64_t n, int64_t d, int64_t shard_num, void* workspace,
                           size_t workspace_bytes, double* out, void* stream);
 
+/* split_selected_rows — replaces operators/split_selected_rows_op.h:24-102 (whose GPU path issues one
+ * cudaMemcpyAsync per row, :83-99): range split of a SelectedRows by `height_sections` (HOST array of
+ * n_sections <= 64 section heights, the op's attribute).  Section of a row = FindOutIdx (:24-32): the
+ * first section whose successor starts above it; rows past the last start land in the last section.
+ * Outputs are laid out section after section, input order kept inside a section:
+ *   out_rows[i]  = row - start of its section, out_value[i,:] = its value row,
+ *   bounds[s]    = first output position of section s, bounds[n_sections] = n (device int64[n_sections+1]).
+ * out_rows doubles as scratch and must not alias rows. */
+int b200emb_split_selected_rows_f32(const int64_t* rows, const float* value, int64_t n, int64_t d,
+                                    const int64_t* height_sections, int64_t n_sections,
+                                    int64_t* out_rows, float* out_value, int64_t* bounds,
+                                    void* workspace, size_t workspace_bytes, void* stream);
+int b200emb_split_selected_rows_f64(const int64_t* rows, const double* value, int64_t n, int64_t d,
+                                    const int64_t* height_sections, int64_t n_sections,
+                                    int64_t* out_rows, double* out_value, int64_t* bounds,
+                                    void* workspace, size_t workspace_bytes, void* stream);
+
+/* extract_rows — replaces operators/extract_rows_op.cc:49-77: Out[n,1] = the SelectedRows' row ids. */
+int b200emb_extract_rows(const int64_t* rows, int64_t n, int64_t* out, void* stream);
+
+/* The sparse weight-decay chain the reference's regularizers append for a SelectedRows gradient
+ * (python/paddle/fluid/regularizer.py:146-170 L2Decay, :226-253 L1Decay, added to the gradient at
+ * :64-69) — extract_rows -> lookup_table -> [sign] -> scale -> elementwise_add — as ONE kernel:
+ *   out[i,:] = addend[i,:] + coeff * f(table[rows[i],:]),  f = identity (mode 0, L2) or sign (mode 1, L1:
+ *   Eigen's sign(), operators/sign_op.h:34), every product and sum rounded on its own like the op chain.
+ * addend == NULL gives the decay term alone (the chain without the final add); out may alias addend.
+ * A row outside [0,height) sets status bit0 (lookup_table_op.h:59-60) and contributes no decay. */
+#define B200EMB_DECAY_L2 0
+#define B200EMB_DECAY_L1 1
+int b200emb_sparse_decay_f32(const float* table, int64_t height, int64_t d, const int64_t* rows,
+                             int64_t n, float coeff, int mode, const float* addend, float* out,
+                             int32_t* status, void* stream);
+int b200emb_sparse_decay_f64(const double* table, int64_t height, int64_t d, const int64_t* rows,
+                             int64_t n, double coeff, int mode, const double* addend, double* out,
+                             int32_t* status, void* stream);
+
 /* Fused compute + exchange for the row-sharded path (no counterpart in the reference, whose
  * multi-device SelectedRows path copies whole blocks with cudaMemcpyPeer: memory/memcpy.cc:65-72).
  * The destinations are device pointers that may live on OTHER GPUs of the box (peer-mapped, e.g.

@@ -283,6 +283,28 @@ def split_selected_rows(rows, value, height_sections):
             for s in range(hs.size)]
 
 
+def extract_rows(rows):
+    """extract_rows_op.cc:49-77: Out[n,1] = the SelectedRows' row ids (duplicates kept)."""
+    return _ids(rows).reshape(-1, 1).copy()
+
+
+def sparse_decay(table, rows, coeff, mode=0, addend=None):
+    """The regularizers' SelectedRows op chain (regularizer.py:146-170 / 226-253 + 64-69):
+    out = [addend +] coeff * f(table[rows]), f = identity (mode 0, L2) or sign (mode 1, L1)."""
+    table = np.ascontiguousarray(table)
+    rows = _ids(rows)
+    v, d = table.shape
+    out = np.empty((rows.size, d), dtype=table.dtype)
+    ct = ctypes.c_float if table.dtype == np.float32 else ctypes.c_double
+    add = None if addend is None else np.ascontiguousarray(addend, dtype=table.dtype)
+    rc = _fn("oracle_sparse_decay_" + _sfx(table.dtype))(
+        _p(table), ctypes.c_int64(v), ctypes.c_int64(d), _p(rows), ctypes.c_int64(rows.size), ct(coeff),
+        ctypes.c_int(mode), None if add is None else _p(add), _p(out))
+    if rc != 0:
+        raise IndexError("sparse_decay: rows[%d] outside [0,%d)" % (-rc - 1, v))
+    return out
+
+
 def gather_selected_rows(per_device):
     """ReduceOpHandle's SelectedRows branch = concat in device order (reduce_and_gather.h:56-93)."""
     return sum_selected_rows(per_device)

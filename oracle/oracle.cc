@@ -422,6 +422,42 @@ void oracle_split_selected_rows_f32(const int64_t* rows, int64_t n, const float*
   }
 }
 
+// Sparse weight decay: the op chain the regularizers append for a SelectedRows gradient
+// (python/paddle/fluid/regularizer.py:146-170 L2Decay, :226-253 L1Decay, then :64-69), op by op:
+//   extract_rows  (extract_rows_op.cc:49-77)   idx = the gradient's row ids, duplicates kept
+//   lookup_table  (lookup_table_op.h:46-63)    decay[i,:] = W[idx[i],:]
+//   sign          (sign_op.h:34, L1 only)      Eigen's scalar_sign_op (third-party Eigen, pinned in
+//                                              cmake/external/eigen.cmake:27 to 917060c3; its real-type
+//                                              functor is Scalar((a > 0) - (a < 0)))
+//   scale         (scale_op.h:53-56)           decay = scale * decay
+//   elementwise_add(grad, decay)               out = grad + decay       (skipped when addend == null)
+// returns 0 or -(k+1) when rows[k] violates lookup_table's range check.
+}  // extern "C"
+namespace {
+template <typename T>
+int64_t SparseDecay(const T* table, int64_t height, int64_t width, const int64_t* rows, int64_t n,
+                    T coeff, int mode, const T* addend, T* out) {
+  std::vector<int64_t> idx(rows, rows + n);                         // extract_rows
+  std::vector<T> decay(static_cast<size_t>(n * width));
+  const int64_t rc = LookupTable<T>(table, height, width, idx.data(), n, -1, decay.data());
+  if (rc != 0) return rc;
+  if (mode == 1)
+    for (auto& x : decay) x = T((x > T(0)) - (x < T(0)));           // sign
+  for (auto& x : decay) x = coeff * x;                              // scale
+  for (int64_t i = 0; i < n * width; ++i) out[i] = addend ? addend[i] + decay[i] : decay[i];
+  return 0;
+}
+}  // namespace
+extern "C" {
+int64_t oracle_sparse_decay_f32(const float* table, int64_t height, int64_t width, const int64_t* rows,
+                                int64_t n, float coeff, int mode, const float* addend, float* out) {
+  return SparseDecay<float>(table, height, width, rows, n, coeff, mode, addend, out);
+}
+int64_t oracle_sparse_decay_f64(const double* table, int64_t height, int64_t width, const int64_t* rows,
+                                int64_t n, double coeff, int mode, const double* addend, double* out) {
+  return SparseDecay<double>(table, height, width, rows, n, coeff, mode, addend, out);
+}
+
 // GatherSelectedRows (multi-device reduce): framework/details/reduce_and_gather.h:56-93
 // = concatenation in device order.  Implemented by repeated oracle_selected_rows_add_to
 // from Python; nothing numeric happens.

@@ -20,7 +20,7 @@ FLUID_LIB_PATH = os.path.join(PKG_DIR, "libb200emb_fluid.so")
 
 NVCC_FLAGS = ["-O3", "-std=c++20", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-fmad=false", "-Xcompiler", "-fPIC", "-shared"]
-KERNEL_SOURCES = ["capi.cu", "sort.cu", "cluster_sort.cu", "gather.cu", "segreduce.cu", "shard.cu", "peer.cu", "noalloc.cu"]
+KERNEL_SOURCES = ["capi.cu", "sort.cu", "cluster_sort.cu", "gather.cu", "segreduce.cu", "shard.cu", "regularize.cu", "peer.cu", "noalloc.cu"]
 
 
 def _nvcc():

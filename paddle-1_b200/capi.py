@@ -34,6 +34,8 @@ EXPORTS = [
     "b200emb_gather_sorted_f32", "b200emb_gather_sorted_f64",
     "b200emb_lookup_table_scatter_f32", "b200emb_merge_add_scatter_f32", "b200emb_segment_scatter_i64",
     "b200emb_split_ids", "b200emb_merge_ids_f32", "b200emb_merge_ids_f64",
+    "b200emb_split_selected_rows_f32", "b200emb_split_selected_rows_f64", "b200emb_extract_rows",
+    "b200emb_sparse_decay_f32", "b200emb_sparse_decay_f64",
     "b200emb_peer_alloc", "b200emb_peer_open", "b200emb_peer_close", "b200emb_peer_free",
 ]
 
@@ -417,6 +419,53 @@ def split_ids(ids, height, shard_num, workspace, status=None):
                                    _ptr(out), _ptr(bounds), _ptr(workspace), ctypes.c_size_t(workspace.numel()),
                                    _ptr(status), _stream()), "split_ids")
     return out[:n], bounds
+
+
+def split_selected_rows(rows, value, height_sections, workspace=None):
+    """Reference split_selected_rows: range split by height_sections (host list).  Returns
+    (out_rows[n] rebased to the section start, out_value[n,d], bounds[len(height_sections)+1]); section s
+    owns output positions [bounds[s], bounds[s+1])."""
+    _need_cuda(rows, value, workspace)
+    n, d = value.shape
+    if workspace is None:
+        workspace = alloc_workspace(n, d, value.element_size(), value.device)
+    hs = (ctypes.c_int64 * len(height_sections))(*[int(h) for h in height_sections])
+    out_rows = torch.empty(max(n, 1), dtype=torch.int64, device=value.device)
+    out_value = torch.empty((n, d), dtype=value.dtype, device=value.device)
+    bounds = torch.zeros(len(height_sections) + 1, dtype=torch.int64, device=value.device)
+    fn = getattr(lib(), "b200emb_split_selected_rows_" + _sfx(value.dtype))
+    _check(fn(_ptr(rows), _ptr(value), ctypes.c_int64(n), ctypes.c_int64(d), hs,
+              ctypes.c_int64(len(height_sections)), _ptr(out_rows), _ptr(out_value), _ptr(bounds),
+              _ptr(workspace), ctypes.c_size_t(workspace.numel()), _stream()), "split_selected_rows")
+    return out_rows[:n], out_value, bounds
+
+
+def extract_rows(rows, out=None):
+    """Reference extract_rows: the SelectedRows' row ids as an int64 tensor [n, 1]."""
+    _need_cuda(rows, out)
+    n = rows.numel()
+    if out is None:
+        out = torch.empty((n, 1), dtype=torch.int64, device=rows.device)
+    _check(lib().b200emb_extract_rows(_ptr(rows), ctypes.c_int64(n), _ptr(out), _stream()), "extract_rows")
+    return out
+
+
+DECAY_L2, DECAY_L1 = 0, 1
+
+
+def sparse_decay(table, rows, coeff, mode=DECAY_L2, addend=None, out=None, status=None):
+    """The regularizers' SelectedRows chain in one kernel: out[i,:] = addend[i,:] + coeff*f(table[rows[i],:])
+    (f = identity for L2, sign for L1); addend=None gives the decay term alone."""
+    _need_cuda(table, rows, addend, out, status)
+    v, d = table.shape
+    n = rows.numel()
+    if out is None:
+        out = torch.empty((n, d), dtype=table.dtype, device=table.device)
+    ct = ctypes.c_float if table.dtype == torch.float32 else ctypes.c_double
+    fn = getattr(lib(), "b200emb_sparse_decay_" + _sfx(table.dtype))
+    _check(fn(_ptr(table), ctypes.c_int64(v), ctypes.c_int64(d), _ptr(rows), ctypes.c_int64(n), ct(coeff),
+              ctypes.c_int(mode), _ptr(addend), _ptr(out), _ptr(status), _stream()), "sparse_decay")
+    return out
 
 
 def merge_ids(x, shard_num, workspace, out=None):

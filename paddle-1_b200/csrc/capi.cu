@@ -286,6 +286,100 @@ int b200emb_merge_ids_f64(const double* x, int64_t n, int64_t d, int64_t shard_n
   return run_permute<double>(x, n, d, shard_num, workspace, workspace_bytes, out, 2, stream);
 }
 
+// ---- split_selected_rows / extract_rows / sparse weight decay (regularize.cu) ---------------------
+}  // extern "C"
+namespace {
+template <typename T>
+int run_split_selected_rows(const int64_t* rows, const T* value, int64_t n, int64_t d,
+                            const int64_t* height_sections, int64_t n_sections, int64_t* out_rows,
+                            T* out_value, int64_t* bounds, void* workspace, size_t workspace_bytes,
+                            void* stream) {
+  if (n_sections < 1 || n_sections > max_sections() || !height_sections || !bounds)
+    return B200EMB_E_INVALID;
+  int rc = check_sizes(n, d, n_sections);
+  if (rc != B200EMB_OK) return rc;
+  for (int64_t j = 0; j < n_sections; ++j)
+    if (height_sections[j] < 0) return B200EMB_E_INVALID;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (n == 0) {
+    cudaError_t e = cudaMemsetAsync(bounds, 0, sizeof(int64_t) * (n_sections + 1), s);
+    return e == cudaSuccess ? B200EMB_OK : fail_cuda(e);
+  }
+  if (!rows || !value || !out_rows || !out_value || out_rows == rows) return B200EMB_E_INVALID;
+  const Workspace L = make_workspace(n, 1, 4);
+  rc = check_workspace(workspace, workspace_bytes, L);
+  if (rc != B200EMB_OK) return rc;
+  char* ws = static_cast<char*>(workspace);
+  const int ns = static_cast<int>(n_sections);
+  cudaError_t e = launch_section_of(rows, n, height_sections, ns, out_rows, s);   // out_rows = scratch
+  if (e != cudaSuccess) return fail_cuda(e);
+  SortedPlan plan;
+  e = launch_plan(out_rows, n, n_sections, ws, L, nullptr, s, &plan);             // stable partition
+  if (e != cudaSuccess) return fail_cuda(e);
+  // sections present (unique keys) pass through bounds' neighbour out_rows for a moment; rebase overwrites
+  e = launch_head_scan(plan, n, static_cast<uint32_t>(n_sections), ws, L, out_rows, nullptr, s);
+  if (e != cudaSuccess) return fail_cuda(e);
+  e = launch_shard_split(out_rows, plan, ws, L, ns, 1, n, static_cast<uint32_t>(n_sections), nullptr,
+                         bounds, nullptr, s);
+  if (e != cudaSuccess) return fail_cuda(e);
+  e = launch_rebase_rows(rows, plan, n, height_sections, ns, out_rows, s);
+  if (e != cudaSuccess) return fail_cuda(e);
+  e = launch_permute_rows<T>(value, plan, reinterpret_cast<const uint32_t*>(ws + L.off_uidx), n, d,
+                             out_value, 0, s);
+  return e == cudaSuccess ? B200EMB_OK : fail_cuda(e);
+}
+
+template <typename T>
+int run_sparse_decay(const T* table, int64_t height, int64_t d, const int64_t* rows, int64_t n, T coeff,
+                     int mode, const T* addend, T* out, int32_t* status, void* stream) {
+  int rc = check_sizes(n, d, height);
+  if (rc != B200EMB_OK) return rc;
+  if (mode != B200EMB_DECAY_L2 && mode != B200EMB_DECAY_L1) return B200EMB_E_INVALID;
+  if (n == 0) return B200EMB_OK;
+  if (!table || !rows || !out) return B200EMB_E_INVALID;
+  cudaError_t e = launch_sparse_decay<T>(table, height, d, rows, n, coeff, mode, addend, out, status,
+                                         static_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? B200EMB_OK : fail_cuda(e);
+}
+}  // namespace
+extern "C" {
+
+int b200emb_split_selected_rows_f32(const int64_t* rows, const float* value, int64_t n, int64_t d,
+                                    const int64_t* height_sections, int64_t n_sections,
+                                    int64_t* out_rows, float* out_value, int64_t* bounds,
+                                    void* workspace, size_t workspace_bytes, void* stream) {
+  return run_split_selected_rows<float>(rows, value, n, d, height_sections, n_sections, out_rows,
+                                        out_value, bounds, workspace, workspace_bytes, stream);
+}
+int b200emb_split_selected_rows_f64(const int64_t* rows, const double* value, int64_t n, int64_t d,
+                                    const int64_t* height_sections, int64_t n_sections,
+                                    int64_t* out_rows, double* out_value, int64_t* bounds,
+                                    void* workspace, size_t workspace_bytes, void* stream) {
+  return run_split_selected_rows<double>(rows, value, n, d, height_sections, n_sections, out_rows,
+                                         out_value, bounds, workspace, workspace_bytes, stream);
+}
+
+int b200emb_extract_rows(const int64_t* rows, int64_t n, int64_t* out, void* stream) {
+  if (n < 0) return B200EMB_E_INVALID;
+  if (n == 0) return B200EMB_OK;
+  if (!rows || !out) return B200EMB_E_INVALID;
+  if (rows == out) return B200EMB_OK;
+  cudaError_t e = cudaMemcpyAsync(out, rows, sizeof(int64_t) * n, cudaMemcpyDeviceToDevice,
+                                  static_cast<cudaStream_t>(stream));
+  return e == cudaSuccess ? B200EMB_OK : fail_cuda(e);
+}
+
+int b200emb_sparse_decay_f32(const float* table, int64_t height, int64_t d, const int64_t* rows,
+                             int64_t n, float coeff, int mode, const float* addend, float* out,
+                             int32_t* status, void* stream) {
+  return run_sparse_decay<float>(table, height, d, rows, n, coeff, mode, addend, out, status, stream);
+}
+int b200emb_sparse_decay_f64(const double* table, int64_t height, int64_t d, const int64_t* rows,
+                             int64_t n, double coeff, int mode, const double* addend, double* out,
+                             int32_t* status, void* stream) {
+  return run_sparse_decay<double>(table, height, d, rows, n, coeff, mode, addend, out, status, stream);
+}
+
 // ---- peer-store variants for the sharded path (destinations may be other GPUs' memory) ----------
 int b200emb_lookup_table_scatter_f32(const float* table, int64_t height, int64_t d, const int64_t* ids,
                                      int64_t n, int64_t padding_idx, const int64_t* seg_start,

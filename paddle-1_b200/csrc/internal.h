@@ -82,6 +82,18 @@ cudaError_t launch_head_scan(const SortedPlan& plan, int64_t n, uint32_t invalid
                              const Workspace& L, int64_t* out_rows, int64_t* n_unique_out,
                              cudaStream_t s);
 
+// regularize.cu
+template <typename T>
+cudaError_t launch_sparse_decay(const T* table, int64_t height, int64_t d, const int64_t* rows, int64_t n,
+                                T coeff, int mode, const T* addend, T* out, int32_t* status,
+                                cudaStream_t s);
+int max_sections();
+cudaError_t launch_section_of(const int64_t* rows, int64_t n, const int64_t* height_sections, int n_sections,
+                              int64_t* out, cudaStream_t s);
+cudaError_t launch_rebase_rows(const int64_t* rows, const SortedPlan& plan, int64_t n,
+                               const int64_t* height_sections, int n_sections, int64_t* out,
+                               cudaStream_t s);
+
 // cluster_sort.cu
 bool cluster_sort_fits(int64_t n);
 cudaError_t launch_cluster_sort(const int64_t* rows, int64_t n, int64_t height, int passes,

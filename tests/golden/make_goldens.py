@@ -113,6 +113,18 @@ G["G10_selected_rows_layout"] = {
     "complete_dims": [10, 100],
 }
 
+# G11  the ops of the sparse regulariser chain (regularizer.py:146-170, 226-253):
+# test_extract_rows_op.py:28-53 (rows with a duplicate come back verbatim, shape [n,1]);
+# test_scale_op.py:38-78 (SelectedRows in/out: value * scale exactly, rows and height kept);
+# test_sign_op.py:23-30 (Out = np.sign(X)).
+G["G11_regulariser_ops"] = {
+    "src": "python/paddle/fluid/tests/unittests/test_{extract_rows,scale,sign}_op.py",
+    "extract_rows": [0, 4, 4, 7], "extract_feature_len": 12,
+    "scale_rows": [0, 4, 7], "scale_height": 10, "scale_row_numel": 12, "scale": 2.0,
+    "dense_scale": -2.3, "dense_shape": [10, 10],
+    "sign_range": [-10, 10], "sign_shape": [10, 10],
+}
+
 if __name__ == "__main__":
     out = os.path.join(os.path.dirname(os.path.abspath(__file__)), "goldens.json")
     with open(out, "w") as f:

@@ -250,3 +250,35 @@ def test_lookup_table_grad_sparse_keeps_duplicates_and_order():
     assert np.array_equal(value, dout)
     dense = oracle.lookup_table_grad_dense(ids, dout, 6)
     assert dense[5].tolist() == [0 + 4, 1 + 5]
+
+
+def test_g11_regulariser_ops(goldens):
+    g = goldens["G11_regulariser_ops"]
+    # test_extract_rows_op.py:28-53
+    assert [r[0] for r in oracle.extract_rows(g["extract_rows"]).tolist()] == g["extract_rows"]
+    rng = np.random.default_rng(11)
+    # test_scale_op.py:38-78 — scale on a SelectedRows: with a table whose row r is in_array[i] the chain
+    # lookup_table -> scale must give in_array * scale exactly
+    rows = g["scale_rows"]
+    table = np.zeros((g["scale_height"], g["scale_row_numel"]), np.float32)
+    in_array = rng.random((len(rows), g["scale_row_numel"])).astype(np.float32)
+    table[rows] = in_array
+    assert (oracle.sparse_decay(table, rows, g["scale"]) == in_array * np.float32(g["scale"])).all()
+    # test_scale_op.py:26-31 (dense, scale -2.3) and test_sign_op.py:23-30 through the same chain
+    x = rng.random(tuple(g["dense_shape"])).astype(np.float32)
+    ident = np.arange(x.shape[0])
+    assert (oracle.sparse_decay(x, ident, g["dense_scale"]) == x * np.float32(g["dense_scale"])).all()
+    lo, hi = g["sign_range"]
+    y = rng.uniform(lo, hi, tuple(g["sign_shape"])).astype(np.float32)
+    y[0, :3] = [0.0, -0.0, np.nan]
+    want = np.sign(y)
+    want[0, 2] = 0.0           # Eigen's (a>0)-(a<0) gives 0 for NaN where numpy propagates it
+    assert (oracle.sparse_decay(y, ident, 1.0, mode=1) == want).all()
+    # the whole chain with the final elementwise_add, duplicates each getting their own decay term
+    grad = rng.standard_normal((4, 12)).astype(np.float32)
+    tab = rng.standard_normal((8, 12)).astype(np.float32)
+    r = np.array(g["extract_rows"])
+    got = oracle.sparse_decay(tab, r, 0.01, 0, addend=grad)
+    assert (got == grad + np.float32(0.01) * tab[r]).all()
+    with pytest.raises(IndexError):
+        oracle.sparse_decay(tab, [8], 0.01)
