@@ -8,7 +8,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 PKG = os.path.dirname(HERE)
 ROOT = os.path.dirname(PKG)
 OUT = os.path.join(PKG, "libb200emb_fluid.so")
-SOURCES = ["lookup_table_op.cu", "sum_op.cu", "sgd_op.cu", "adam_op.cu", "adagrad_op.cu", "runner.cu"]
+SOURCES = ["lookup_table_op.cu", "sum_op.cu", "sgd_op.cu", "adam_op.cu", "adagrad_op.cu", "split_ids_op.cu",
+           "split_selected_rows_op.cu", "runner.cu"]
 
 
 def _newer(target, deps):

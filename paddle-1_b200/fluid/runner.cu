@@ -71,7 +71,7 @@ fw::VariableNameMap ParseSlots(const char* spec) {
   }
   return m;
 }
-// "name:kind:value;..."  kinds: b(ool) i(nt) l(ong) f(loat) s(tring)
+// "name:kind:value;..."  kinds: b(ool) i(nt) l(ong) f(loat) s(tring) v(ector<int>, '|'-separated)
 fw::AttributeMap ParseAttrs(const char* spec) {
   fw::AttributeMap m;
   std::stringstream ss(spec ? spec : "");
@@ -84,6 +84,13 @@ fw::AttributeMap ParseAttrs(const char* spec) {
     else if (kind == "i") m[name] = std::stoi(val);
     else if (kind == "l") m[name] = static_cast<int64_t>(std::stoll(val));
     else if (kind == "f") m[name] = std::stof(val);
+    else if (kind == "v") {
+      std::vector<int> v;
+      std::stringstream vs(val);
+      std::string x;
+      while (std::getline(vs, x, '|')) if (!x.empty()) v.push_back(std::stoi(x));
+      m[name] = v;
+    }
     else m[name] = val;
   }
   return m;
@@ -93,7 +100,8 @@ fw::AttributeMap ParseAttrs(const char* spec) {
 const char* KeySlot(const std::string& type) {
   if (type == "lookup_table" || type == "lookup_table_grad") return "W";   // lookup_table_op.cc:53-57
   if (type == "sgd" || type == "adam" || type == "adagrad") return "Param";  // sgd_op.cc:44-48, adam_op.cc:76-81
-  return "X";                                                              // sum_op.cc:67-127
+  if (type == "split_ids") return "Ids";                                   // split_ids_op.cc:57-63
+  return "X";                                                              // sum_op.cc:67-127, merge_ids_op.cc:101-107
 }
 }  // namespace
 

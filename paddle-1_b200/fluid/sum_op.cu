@@ -95,6 +95,11 @@ class SumB200Kernel : public framework::OpKernel<T> {
       if (total == 0) return;
       int64_t* out_rows = out->mutable_rows()->CUDAMutableData(place);
       const int64_t d = out_value->numel() / total;
+      // Runtime InferShape (SumOp::InferShape, sum_op.cc:33-64, through RuntimeInferShapeContext::SetDim,
+      // operator.cc:608-622) gives Out the complete dims of the inputs, i.e. their height, before the kernel
+      // runs; the mini runner has no InferShape pass, so the same assignment happens here.
+      for (int i = 0; i < N; ++i)
+        if (get(i).rows().size() > 0) { out->set_height(get(i).height()); break; }
       int64_t offset = 0;
       for (int i = 0; i < N; ++i) {
         const SelectedRows& s = get(i);

@@ -26,6 +26,10 @@ OP_SLOTS = {
     "adam": (["Param", "Grad", "LearningRate", "Moment1", "Moment2", "Beta1Pow", "Beta2Pow"],
              ["ParamOut", "Moment1Out", "Moment2Out"]),
     "adagrad": (["Param", "Grad", "Moment", "LearningRate"], ["ParamOut", "MomentOut"]),
+    "split_ids": (["Ids"], ["Out"]),
+    "merge_ids": (["Ids", "X"], ["Out"]),
+    "split_selected_rows": (["X"], ["Out"]),
+    "extract_rows": (["X"], ["Out"]),
 }
 # attributes with their defaults (OpAttrChecker defaults: lookup_table_op.cc:71-83, adam_op.cc:99-112)
 OP_ATTRS = {
@@ -35,6 +39,8 @@ OP_ATTRS = {
     "sgd": {},
     "adam": {"beta1": ("f", 0.9), "beta2": ("f", 0.999), "epsilon": ("f", 1.0e-8)},
     "adagrad": {"epsilon": ("f", 1.0e-6)},
+    "split_ids": {}, "merge_ids": {}, "extract_rows": {},
+    "split_selected_rows": {"height_sections": ("v", [])},
 }
 
 
@@ -191,6 +197,8 @@ class Operator:
                 val = "1" if val else "0"
             elif kind == "f":
                 val = repr(float(val))
+            elif kind == "v":
+                val = "|".join(str(int(x)) for x in val)
             attrs.append("%s:%s:%s" % (name, kind, val))
         _check(lib().fl_op_run(scope._h, self.type.encode(), slots(self.inputs), slots(self.outputs),
                                ";".join(attrs).encode(), place.device))

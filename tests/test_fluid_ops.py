@@ -248,3 +248,142 @@ def test_sparse_adagrad_op(core):
     assert result_array[5, 8] == pytest.approx(get_out(5.0, 2.0, 0.0, 2.0, 2.0), abs=1e-5)
     assert result_array[rows[2], 1] == pytest.approx(get_out(5.0, 2.0, 1.0, 3.0, 2.0), abs=1e-5)
     assert result_array[rows[2], 8] == pytest.approx(get_out(5.0, 2.0, 4.0, 18.0, 2.0), abs=1e-5)
+
+
+def test_sharding_kernels_are_registered(core):
+    # CPU-only (`PADDLE_THROW` on GPU) or one-memcpy-per-row in the reference; CUDA kernels here
+    for op in ("split_ids", "merge_ids", "split_selected_rows", "extract_rows"):
+        assert core.registered_kernels(op) == 2
+
+
+def test_split_ids_op_lod_tensor(core):
+    # TestSplitIdsOp (test_split_ids_op.py:25-37)
+    place = core.CUDAPlace(0)
+    scope = core.Scope()
+    ids = np.array([[0], [2], [2], [3], [5], [5], [6]]).astype("int64")
+    scope.var("Ids").get_tensor().set(ids, place)
+    outs = ["out0", "out1", "out2"]
+    for name in outs:
+        scope.var(name).get_tensor()
+    core.Operator("split_ids", Ids="Ids", Out=outs).run(scope, place)
+    want = [[[0], [3], [6]], [], [[2], [2], [5], [5]]]
+    for name, w in zip(outs, want):
+        got = np.array(scope.var(name).get_tensor())
+        assert got.shape == (len(w), 1) and got.reshape(-1).tolist() == [x[0] for x in w]
+    # a larger batch against the oracle
+    big = np.random.default_rng(0).integers(0, 1 << 31, (50000, 1)).astype("int64")
+    scope.var("Ids").get_tensor().set(big, place)
+    outs = ["s%d" % i for i in range(7)]
+    for name in outs:
+        scope.var(name).get_tensor()
+    core.Operator("split_ids", Ids="Ids", Out=outs).run(scope, place)
+    for name, w in zip(outs, oracle.split_ids(big.reshape(-1), 7)):
+        assert np.array_equal(np.array(scope.var(name).get_tensor()).reshape(-1), w)
+
+
+def test_split_ids_op_selected_rows(core):
+    # TestSpliteIds (test_split_ids_op.py:40-87), run 3 times like the reference test
+    place = core.CUDAPlace(0)
+    scope = core.Scope()
+    rows, height, row_numel = [0, 5, 7, 4, 9], 20, 2
+    x = scope.var("X").get_selected_rows()
+    x.set_rows(rows)
+    x.set_height(height)
+    arr = np.array([[r + j for j in range(row_numel)] for r in rows], np.float32)
+    x.get_tensor().set(arr, place)
+    outs_name = ["out%d" % i for i in range(3)]
+    outs = [scope.var(n).get_selected_rows() for n in outs_name]
+    op = core.Operator("split_ids", Ids="X", Out=outs_name)
+    for _ in range(3):
+        op.run(scope, place)
+        for out, expect in zip(outs, [[0, 9], [7, 4], [5]]):
+            assert out.rows() == expect and out.height() == height
+            got = np.array(out.get_tensor())
+            for j, row in enumerate(expect):
+                assert got[j, 0] == float(row) and got[j, 1] == float(row + 1)
+    # duplicated row ids: every copy takes the LAST occurrence's value (id_to_index, split_ids_op.h:71-76)
+    rows = [3, 1, 3, 4, 1, 3]
+    x.set_rows(rows)
+    arr = np.arange(12, dtype=np.float32).reshape(6, 2)
+    x.get_tensor().set(arr, place)
+    op.run(scope, place)
+    for out, (wr, wv) in zip(outs, oracle.split_ids_selected_rows(rows, arr, 3)):
+        assert out.rows() == wr.tolist()
+        assert np.array_equal(np.array(out.get_tensor()).reshape(-1, 2), wv)
+
+
+def test_merge_ids_op(core):
+    # TestMergeIdsOp (test_merge_ids_op.py:22-34)
+    place = core.CUDAPlace(0)
+    scope = core.Scope()
+    ids = np.array([[0], [2], [2], [3], [5], [5], [6]]).astype("int64")
+    x0 = np.array([[0.1, 0.2], [0.2, 0.3], [0.3, 0.4]]).astype("float32")
+    x1 = np.zeros((0, 2), "float32")
+    x2 = np.array([[0.4, 0.5], [0.4, 0.5], [0.5, 0.6], [0.5, 0.6]]).astype("float32")
+    want = np.array([[0.1, 0.2], [0.4, 0.5], [0.4, 0.5], [0.2, 0.3], [0.5, 0.6], [0.5, 0.6], [0.3, 0.4]], "float32")
+    scope.var("Ids").get_tensor().set(ids, place)
+    for name, x in (("x0", x0), ("x1", x1), ("x2", x2)):
+        scope.var(name).get_tensor().set(x, place)
+    core.Operator("merge_ids", Ids="Ids", X=["x0", "x1", "x2"], Out="Out").run(scope, place)
+    assert np.array_equal(np.array(scope.var("Out").get_tensor()), want)
+    # a shard with the wrong number of rows: "after merge, all data in x_tensor should be used"
+    scope.var("x2").get_tensor().set(x2[:3], place)
+    scope.var("x0").get_tensor().set(np.concatenate([x0, x0[:1]]), place)
+    with pytest.raises(core.FluidLiteError):
+        core.Operator("merge_ids", Ids="Ids", X=["x0", "x1", "x2"], Out="Out").run(scope, place)
+
+
+def test_split_selected_rows_op(core):
+    # TestSpliteSelectedRows.check_with_place / check_grad_with_place (test_split_selected_rows_op.py:36-126)
+    place = core.CUDAPlace(0)
+    scope = core.Scope()
+    rows, height, row_numel = [0, 5, 7, 4, 20], 20, 2
+    x = scope.var("X").get_selected_rows()
+    x.set_rows(rows)
+    x.set_height(height)
+    arr = np.ones((len(rows), row_numel)).astype("float32")
+    arr[0, 0], arr[2, 1], arr[4, 1] = 2.0, 4.0, 8.0
+    x.get_tensor().set(arr, place)
+    height_sections = [5, 5, 5, 5, 3]
+    outs_name = ["out%d" % i for i in range(len(height_sections))]
+    outs = [scope.var(n).get_selected_rows() for n in outs_name]
+    core.Operator("split_selected_rows", X="X", Out=outs_name, height_sections=height_sections).run(scope, place)
+    assert outs[0].rows() == [0, 4] and outs[1].rows() == [0, 2] and outs[4].rows() == [0]
+    assert outs[2].rows() == [] and outs[3].rows() == []
+    assert outs[0].height() == height_sections[0] and outs[4].height() == height_sections[4]
+    assert np.array(outs[0].get_tensor())[0, 0] == 2.0
+    assert np.array(outs[1].get_tensor())[1, 1] == 4.0
+    assert np.array(outs[4].get_tensor())[0, 1] == 8.0
+    # its gradient is `sum` over the outputs' gradients (split_selected_rows_op.cc:64-77)
+    g0 = scope.var("out0@GRAD").get_selected_rows()
+    g0.set_rows([0, 5])
+    g0.set_height(10)
+    a0 = np.ones((2, row_numel)).astype("float32")
+    a0[0, 0] = 2.0
+    g0.get_tensor().set(a0, place)
+    g1 = scope.var("out1@GRAD").get_selected_rows()
+    g1.set_rows([2, 0])
+    g1.set_height(10)
+    a1 = np.ones((2, row_numel)).astype("float32")
+    a1[0, 1] = 4.0
+    g1.get_tensor().set(a1, place)
+    xg = scope.var("X@GRAD").get_selected_rows()
+    core.Operator("sum", X=["out0@GRAD", "out1@GRAD"], Out="X@GRAD").run(scope, place)
+    assert xg.rows() == [0, 5, 2, 0] and xg.height() == 10
+    got = np.array(xg.get_tensor())
+    assert got[0, 0] == 2.0 and got[2, 1] == 4.0
+
+
+def test_extract_rows_op(core):
+    # TestExtractRows (test_extract_rows_op.py:26-53)
+    place = core.CUDAPlace(0)
+    scope = core.Scope()
+    rows, feature_len = [0, 4, 4, 7], 12
+    x = scope.var("X").get_selected_rows()
+    x.set_height(len(rows))
+    x.set_rows(rows)
+    x.get_tensor().set(np.ones((len(rows), feature_len)).astype("float32"), place)
+    scope.var("Out").get_tensor()
+    core.Operator("extract_rows", X="X", Out="Out").run(scope, place)
+    result = np.array(scope.var("Out").get_tensor())
+    assert result.shape == (4, 1) and [e[0] for e in result] == rows
