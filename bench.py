@@ -221,8 +221,8 @@ def run_single(args):
         capi.sparse_sgd(table, ids[b], dout[b], lr, ws[b], capi.PLAN_READY, status)
         main.wait_stream(side)
 
-    # gather, sort plan, chunk reduce, fixup (fast-mode SGD finds the run heads itself: no head scan)
-    kernels_per_step = 1 + capi.plan_kernel_count(n, v) + 2
+    # gather, sort plan, chunk reduce (fast-mode SGD finds the run heads itself: no head scan)
+    kernels_per_step = 1 + capi.plan_kernel_count(n, v) + 1
 
     graphs = []
     with torch.cuda.stream(main):
@@ -336,14 +336,14 @@ def run_single(args):
     if t_gather >= t_update:
         dom = {"kernel": "k_gather (lookup_table fwd)", "bytes": bytes_["fwd"], "t": t_gather}
     else:
-        dom = {"kernel": "k_chunk_reduce+k_fixup (fused MergeAdd+SGD)", "bytes": bytes_["upd"], "t": t_update}
+        dom = {"kernel": "k_chunk_reduce (fused MergeAdd+SGD)", "bytes": bytes_["upd"], "t": t_update}
     achieved = dom["bytes"] / dom["t"] / 1e9
     # DRAM traffic of the same kernel(s) from the committed `ncu --set full` capture (profiles/), per launch
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "r1_ncu_full_summary.json")) as f:
             prof = json.load(f)
-        keys = ["k_gather"] if dom["kernel"].startswith("k_gather") else ["k_chunk_reduce", "k_fixup"]
+        keys = ["k_gather"] if dom["kernel"].startswith("k_gather") else ["k_chunk_reduce"]
         traffic = sum(v["dram_traffic_bytes_per_launch"] for k, v in prof.items() if any(k.startswith(q) for q in keys))
     except Exception:
         traffic = None

@@ -57,6 +57,16 @@ __device__ __forceinline__ void load_vec_stream(const T* __restrict__ p, T (&dst
     dst[0] = __ldg(p);
   }
 }
+// read of data another CTA of the same grid has just published (after a fence): L2 only
+template <typename T, bool VEC>
+__device__ __forceinline__ void load_vec_cg(const T* p, T (&dst)[Epv<T, VEC>::value]) {
+  if constexpr (VEC) {
+    const int4 raw = __ldcg(reinterpret_cast<const int4*>(p));
+    *reinterpret_cast<int4*>(dst) = raw;
+  } else {
+    dst[0] = __ldcg(p);
+  }
+}
 template <typename T, bool VEC>
 __device__ __forceinline__ void store_vec(T* p, const T (&src)[Epv<T, VEC>::value]) {
   if constexpr (VEC) {

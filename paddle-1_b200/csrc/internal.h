@@ -35,9 +35,7 @@ struct Workspace {
   size_t off_uidx;        // u32 [n]   unique index of each sorted position
   size_t off_seg_start;   // u32 [n+1] first sorted position of each unique row
   // carries of the chunked reduce
-  size_t off_cta_flags;   // u32 [max_ctas]
-  size_t off_cta_tail_key;   // u32 [max_ctas]
-  size_t off_cta_tail_eref;  // u32 [max_ctas]
+  size_t off_cta_arrive;  // u32 [max_ctas]  chain arrival counters: cleared by every plan, left at zero by every reduce
   size_t off_cta_head;    // T [max_ctas][d]
   size_t off_cta_tail;    // T [max_ctas][d]
   size_t total;

@@ -10,14 +10,15 @@
 // so merged gradient rows never travel through HBM: each input row is read once, each touched
 // parameter row is read and written once.
 //
-// FAST mode (k_chunk_reduce + k_fixup): the sorted element range is cut into equal chunks, one
+// FAST mode (k_chunk_reduce): the sorted element range is cut into equal chunks, one
 // per lane group, so work is balanced no matter how skewed the ids are (a Zipf head id owns
 // 10-25% of all rows).  A group walks its chunk with kBatch independent row loads in flight;
 // segments that close inside the chunk are consumed immediately.  Segments cut by a chunk
 // boundary leave partial sums in shared memory, are combined across the CTA's groups in fixed
-// order, and — if they also cross the CTA boundary — leave one carry row per CTA for k_fixup.
-// No atomics anywhere: the summation tree is fixed by (N, D) alone, hence run-to-run
-// deterministic.
+// order, and — if they also cross the CTA boundary — leave one carry row per CTA; the last CTA
+// of such a chain to finish (an integer arrival counter, nobody waits) sums the chain's carries in
+// a fixed order.  No floating-point atomics anywhere: the summation tree is fixed by (N, D) alone,
+// hence run-to-run deterministic.
 //
 // DETERMINISTIC mode (k_segment_det): one lane group per unique row walks its duplicates in input
 // order (the stable sort keeps it) with separately rounded IEEE operations, reproducing the
@@ -33,7 +34,6 @@ namespace b200emb {
 namespace {
 
 constexpr uint32_t kHead = 1u, kTail = 2u, kThrough = 4u;             // per-group flags
-constexpr uint32_t kCtaHead = 1u, kCtaHeadThrough = 2u, kCtaTail = 4u;  // per-CTA flags
 
 template <typename T>
 struct Params {
@@ -53,9 +53,26 @@ struct Params {
 
 template <typename T>
 struct Carry {
-  uint32_t* flags; uint32_t* tail_key; uint32_t* tail_eref;
-  T* head; T* tail;
+  uint32_t* arrive;   // [ctas] arrivals at the chain that STARTS in this CTA; zero between launches
+  T* head; T* tail;   // [ctas][d] partial sums of the segment entering / leaving each CTA
 };
+
+// Largest b in [lo, hi) with pred(b) true, for a predicate that is true on [lo, b] and false on
+// (b, hi] (pred(lo) true and pred(hi) false are known, not evaluated).  One warp, 32 probes per
+// memory round trip: a chain of any length is bracketed in <= 4 round trips.
+template <class Pred>
+__device__ __forceinline__ int warp_last_true(int lo, int hi, int lane, Pred pred) {
+  while (hi - lo > 1) {
+    const int step = (hi - lo + 31) / 32;
+    const int p = lo + step * (lane + 1);
+    const bool t = p < hi ? pred(p) : false;
+    const uint32_t f = __ballot_sync(0xffffffffu, !t);   // lane 31 probes >= hi: never empty
+    const int i = __ffs(f) - 1;
+    hi = min(hi, lo + step * (i + 1));
+    lo = lo + step * i;
+  }
+  return lo;
+}
 
 template <typename T, int NV, int EPV>
 __device__ __forceinline__ void zero_acc(T (&a)[NV][EPV]) {
@@ -170,6 +187,80 @@ __device__ __forceinline__ void consume(const Params<T>& P, uint32_t key, uint32
   apply_state<T, OP, LPR, NV, VEC>(P, key, eref, col0, l, acc, st);
 }
 
+// Closes one chain: the segment that leaves CTA `c` (tail carry) and enters the next `len` CTAs
+// (head carries).  Run by the LAST CTA of the chain to arrive, with the whole CTA: the lane
+// groups sum the head rows strided by group with all loads in flight, group 0 adds the per-group
+// partials to the tail in group order — the summation order depends on (N, D) alone, not on
+// which CTA happens to arrive last.
+template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
+__device__ __forceinline__ void close_chain(int c, int len, uint32_t key, uint32_t eref,
+                                            const Params<T>& P, const Carry<T>& C, T* s_part) {
+  constexpr int EPV = Epv<T, VEC>::value;
+  constexpr int GPC = kBlock / LPR;
+  constexpr int COLS = LPR * NV * EPV;
+  constexpr int kRows = NV == 1 ? 8 : 4;  // head rows in flight per group
+  using A = Arith<T>;
+  const int tid = threadIdx.x, g = tid / LPR, l = tid % LPR;
+  const int d = P.d;
+  for (int col0 = 0; col0 < d; col0 += COLS) {
+    T sum[NV][EPV];
+    if (g == 0) {  // tail row: issued before the head rows so the loads overlap
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        const int col = col0 + (l + k * LPR) * EPV;
+        if (col < d) load_vec_cg<T, VEC>(C.tail + static_cast<int64_t>(c) * d + col, sum[k]);
+        else {
+#pragma unroll
+          for (int e = 0; e < EPV; ++e) sum[k][e] = T(0);
+        }
+      }
+    }
+    T part[NV][EPV];
+    zero_acc<T, NV, EPV>(part);
+    for (int r0 = g; r0 < len; r0 += GPC * kRows) {
+      T h[kRows][NV][EPV];
+#pragma unroll
+      for (int q = 0; q < kRows; ++q) {
+        const int r = r0 + q * GPC;
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+          const int col = col0 + (l + k * LPR) * EPV;
+          if (r < len && col < d)
+            load_vec_cg<T, VEC>(C.head + static_cast<int64_t>(c + 1 + r) * d + col, h[q][k]);
+          else {
+#pragma unroll
+            for (int e = 0; e < EPV; ++e) h[q][k][e] = T(0);
+          }
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < kRows; ++q)
+        if (r0 + q * GPC < len) {
+#pragma unroll
+          for (int k = 0; k < NV; ++k)
+#pragma unroll
+            for (int e = 0; e < EPV; ++e) part[k][e] = A::add(part[k][e], h[q][k][e]);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < NV; ++k)
+#pragma unroll
+      for (int e = 0; e < EPV; ++e) s_part[g * COLS + (l + k * LPR) * EPV + e] = part[k][e];
+    __syncthreads();
+    if (g == 0) {
+      const int used = min(len, GPC);
+      for (int j = 0; j < used; ++j)
+#pragma unroll
+        for (int k = 0; k < NV; ++k)
+#pragma unroll
+          for (int e = 0; e < EPV; ++e)
+            sum[k][e] = A::add(sum[k][e], s_part[j * COLS + (l + k * LPR) * EPV + e]);
+      consume<T, OP, LPR, NV, VEC>(P, key, eref, col0, l, sum);
+    }
+    __syncthreads();
+  }
+}
+
 // ------------------------------------------------------------------------------------------
 template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
 __global__ void __launch_bounds__(kBlock, 2)
@@ -187,7 +278,8 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
   uint32_t* s_key = reinterpret_cast<uint32_t*>(s_tail + GPC * COLS);  // [GPC*chunk]
   uint32_t* s_perm = s_key + GPC * chunk;
   __shared__ uint32_t s_flags[GPC];
-  __shared__ uint32_t s_prev_key, s_next_key, s_cta_flags;
+  __shared__ uint32_t s_prev_key, s_next_key;
+  __shared__ int s_before, s_after, s_nfix, s_fix_c[2], s_fix_len[2];
 
   const int tid = threadIdx.x, g = tid / LPR, l = tid % LPR;
   const int d = P.d;
@@ -200,9 +292,29 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
   if (tid == 0) {
     s_prev_key = cta_start > 0 ? skey[cta_start - 1] : kNoKey;
     s_next_key = cta_start + cta_count < n ? skey[cta_start + cta_count] : kNoKey;
-    s_cta_flags = 0;
   }
   __syncthreads();
+
+  // ---- chains: segments cut by CTA boundaries, known from the keys alone ------------------------
+  // A chain is one segment spread over consecutive CTAs: it LEAVES the CTA where it starts (tail
+  // carry) and ENTERS the following ones (head carries).  Every member counts itself in at
+  // arrive[first CTA of the chain]; the member that arrives last closes the chain (close_chain).
+  // No CTA ever waits for another one.  The chain's extent is found by probing the sorted keys at
+  // the CTA boundaries: the first 32 probes are issued here and only read after the main loop.
+  const int lane = tid & 31, warp = tid >> 5;
+  const int cta = blockIdx.x, num_ctas = gridDim.x;
+  const int64_t stride = static_cast<int64_t>(GPC) * chunk;          // sorted elements per CTA
+  const uint32_t k_first = s_key[0], k_last = s_key[cta_count - 1];
+  const bool has_head = s_prev_key == k_first;                        // a segment enters from CTA cta-1
+  const bool through = has_head && k_last == k_first && s_next_key == k_first;   // ... and runs on past this CTA
+  const bool has_tail = !through && s_next_key == k_last;             // a segment that starts here leaves
+  // enters(j): the chain's segment enters CTA j from CTA j-1;   member(j): CTA j starts inside it
+  const auto enters = [&](int j) { return j >= 1 && __ldg(skey + j * stride - 1) == k_first; };
+  const uint32_t k_fwd = through ? k_first : k_last;
+  const auto member = [&](int j) { return j < num_ctas && __ldg(skey + j * stride) == k_fwd; };
+  bool probe = false;
+  if (warp == 0 && has_head) probe = enters(cta - 1 - lane);
+  if (warp == 1 && (through || has_tail)) probe = member(cta + 1 + lane);
 
   const int gs = g * chunk;
   const int ge = min(gs + chunk, cta_count);
@@ -320,11 +432,6 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
           const int col = col0 + (l + k * LPR) * EPV;
           if (col < d) store_vec<T, VEC>(C.tail + static_cast<int64_t>(blockIdx.x) * d + col, sum[k]);
         }
-        if (l == 0) {
-          C.tail_key[blockIdx.x] = tail_key;
-          C.tail_eref[blockIdx.x] = tail_eref;
-          atomicOr(&s_cta_flags, kCtaTail);
-        }
       } else {
         consume<T, OP, LPR, NV, VEC>(P, tail_key, tail_eref, col0, l, sum);
       }
@@ -353,120 +460,56 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
         const int col = col0 + (l + k * LPR) * EPV;
         if (col < d) store_vec<T, VEC>(C.head + static_cast<int64_t>(blockIdx.x) * d + col, sum[k]);
       }
-      if (l == 0) atomicOr(&s_cta_flags, kCtaHead | (to_end ? kCtaHeadThrough : 0u));
     }
     __syncthreads();
   }
-  if (tid == 0) C.flags[blockIdx.x] = s_cta_flags;
-}
+  if (num_ctas == 1) return;
 
-// One CTA per chunk-CTA boundary.  A CTA whose predecessor kernel left a tail carry owns the
-// segment.  Round trip 1: every thread reads one following CTA's flag word (256 per sweep) and
-// warp ballots find the chain length L (how many following CTAs contributed a head).  Round
-// trip 2: the lane groups sum the L head rows, strided by group, with all loads in flight, and
-// group 0 adds the per-group partials to the tail in group order.  A hot id spanning hundreds
-// of CTAs therefore costs a few memory round trips instead of one per carry row.  CTAs without
-// a tail exit at once.
-template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
-__global__ void __launch_bounds__(kBlock)
-k_fixup(int num_ctas, Params<T> P, Carry<T> C) {
-  constexpr int EPV = Epv<T, VEC>::value;
-  constexpr int GPC = kBlock / LPR;
-  constexpr int COLS = LPR * NV * EPV;
-  constexpr int kRows = NV == 1 ? 8 : 4;  // head rows in flight per group
-  constexpr int kWarps = kBlock / 32;
-  using A = Arith<T>;
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  T* s_part = reinterpret_cast<T*>(smem_raw);  // [GPC][COLS]
-  __shared__ int s_stop[kWarps];               // per warp: first index where the chain ends, or -1
-  __shared__ int s_stop_has[kWarps];
-  const int c = blockIdx.x;
-  const int tid = threadIdx.x, g = tid / LPR, l = tid % LPR, lane = tid & 31, warp = tid >> 5;
-  const int d = P.d;
-  // own flag and the first sweep of followers are fetched together
-  const uint32_t own = C.flags[c];
-  int len = 0;
-  bool first = true;
-  for (int base = c + 1;; base += kBlock) {
-    const int j = base + tid;
-    const uint32_t f = j < num_ctas ? C.flags[j] : 0u;
-    if (first && !(own & kCtaTail)) return;
-    first = false;
-    const bool has = (f & kCtaHead) != 0;
-    const bool cont = has && (f & kCtaHeadThrough) != 0;
-    const uint32_t stop = __ballot_sync(0xffffffffu, !cont);
-    const int sl = stop ? __ffs(stop) - 1 : -1;
-    const int sl_has = __shfl_sync(0xffffffffu, has ? 1 : 0, sl < 0 ? 0 : sl);
-    if (lane == 0) {
-      s_stop[warp] = sl < 0 ? -1 : warp * 32 + sl;
-      s_stop_has[warp] = sl_has;
-    }
-    __syncthreads();
-    int found = -1, found_has = 0;
-#pragma unroll
-    for (int w = kWarps - 1; w >= 0; --w)
-      if (s_stop[w] >= 0) { found = s_stop[w]; found_has = s_stop_has[w]; }
-    __syncthreads();
-    if (found >= 0) { len += found + found_has; break; }
-    len += kBlock;
+  // ---- arrivals -----------------------------------------------------------------------------------
+  __threadfence();                       // this CTA's carry rows are visible before it counts itself in
+  if (warp == 0 && has_head) {           // CTAs of the chain before this one
+    const uint32_t stop = __ballot_sync(0xffffffffu, !probe);
+    int before = stop ? __ffs(stop) : 0;
+    if (!stop)                           // longer than 32: enters(cta - m) is true for m <= 32, false at m = cta
+      before = 1 + warp_last_true(32, cta, lane, [&](int m) { return enters(cta - m); });
+    if (lane == 0) s_before = before;
   }
-  const uint32_t key = C.tail_key[c], eref = C.tail_eref[c];
-  for (int col0 = 0; col0 < d; col0 += COLS) {
-    T sum[NV][EPV];
-    if (g == 0) {  // tail row: issued before the head rows so the loads overlap
-#pragma unroll
-      for (int k = 0; k < NV; ++k) {
-        const int col = col0 + (l + k * LPR) * EPV;
-        if (col < d) load_vec<T, VEC>(C.tail + static_cast<int64_t>(c) * d + col, sum[k]);
-        else {
-#pragma unroll
-          for (int e = 0; e < EPV; ++e) sum[k][e] = T(0);
-        }
+  if (warp == 1 && (through || has_tail)) {   // CTAs of the chain after this one
+    const uint32_t stop = __ballot_sync(0xffffffffu, !probe);
+    int after = stop ? __ffs(stop) - 1 : 0;
+    if (!stop)
+      after = warp_last_true(32, num_ctas - cta, lane, [&](int m) { return member(cta + m); });
+    if (lane == 0) s_after = after;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    int nfix = 0;
+    if (has_head) {
+      const int c0 = cta - s_before, members = s_before + (through ? s_after : 0) + 1;
+      if (atomicAdd(C.arrive + c0, 1u) == static_cast<uint32_t>(members - 1)) {
+        s_fix_c[nfix] = c0;
+        s_fix_len[nfix++] = members - 1;
       }
     }
-    T part[NV][EPV];
-    zero_acc<T, NV, EPV>(part);
-    for (int r0 = g; r0 < len; r0 += GPC * kRows) {
-      T h[kRows][NV][EPV];
-#pragma unroll
-      for (int q = 0; q < kRows; ++q) {
-        const int r = r0 + q * GPC;
-#pragma unroll
-        for (int k = 0; k < NV; ++k) {
-          const int col = col0 + (l + k * LPR) * EPV;
-          if (r < len && col < d)
-            load_vec<T, VEC>(C.head + static_cast<int64_t>(c + 1 + r) * d + col, h[q][k]);
-          else {
-#pragma unroll
-            for (int e = 0; e < EPV; ++e) h[q][k][e] = T(0);
-          }
-        }
+    if (has_tail) {
+      if (atomicAdd(C.arrive + cta, 1u) == static_cast<uint32_t>(s_after)) {
+        s_fix_c[nfix] = cta;
+        s_fix_len[nfix++] = s_after;
       }
-#pragma unroll
-      for (int q = 0; q < kRows; ++q)
-        if (r0 + q * GPC < len) {
-#pragma unroll
-          for (int k = 0; k < NV; ++k)
-#pragma unroll
-            for (int e = 0; e < EPV; ++e) part[k][e] = A::add(part[k][e], h[q][k][e]);
-        }
     }
-#pragma unroll
-    for (int k = 0; k < NV; ++k)
-#pragma unroll
-      for (int e = 0; e < EPV; ++e) s_part[g * COLS + (l + k * LPR) * EPV + e] = part[k][e];
-    __syncthreads();
-    if (g == 0) {
-      const int used = min(len, GPC);
-      for (int j = 0; j < used; ++j)
-#pragma unroll
-        for (int k = 0; k < NV; ++k)
-#pragma unroll
-          for (int e = 0; e < EPV; ++e)
-            sum[k][e] = A::add(sum[k][e], s_part[j * COLS + (l + k * LPR) * EPV + e]);
-      consume<T, OP, LPR, NV, VEC>(P, key, eref, col0, l, sum);
-    }
-    __syncthreads();
+    s_nfix = nfix;
+  }
+  __syncthreads();
+  const int nfix = s_nfix;
+  if (nfix == 0) return;
+  __threadfence();                       // the other members' carry rows, published before their arrivals
+  for (int f = 0; f < nfix; ++f) {
+    const int c0 = s_fix_c[f];
+    const bool own_tail = c0 == cta;     // the chain that starts here; otherwise the one that entered
+    close_chain<T, OP, LPR, NV, VEC>(c0, s_fix_len[f], own_tail ? k_last : k_first,
+                                     static_cast<uint32_t>(own_tail ? cta_start + cta_count - 1 : cta_start),
+                                     P, C, s_head);
+    if (tid == 0) C.arrive[c0] = 0;      // ready for the next launch on this workspace
   }
 }
 
@@ -561,9 +604,7 @@ cudaError_t launch_op(const SortedPlan& plan, const T* value, int64_t n, int64_t
   Params<T> P{a.param, a.moment1, a.moment2, a.lr, a.beta1_pow, a.beta2_pow,
               a.beta1, a.beta2, a.epsilon, a.uidx, static_cast<int>(d),
               static_cast<uint32_t>(height), a.shard_bounds, a.shard_dst, a.shards};
-  Carry<T> C{reinterpret_cast<uint32_t*>(ws + L.off_cta_flags),
-             reinterpret_cast<uint32_t*>(ws + L.off_cta_tail_key),
-             reinterpret_cast<uint32_t*>(ws + L.off_cta_tail_eref),
+  Carry<T> C{reinterpret_cast<uint32_t*>(ws + L.off_cta_arrive),
              reinterpret_cast<T*>(ws + L.off_cta_head), reinterpret_cast<T*>(ws + L.off_cta_tail)};
   bool aligned = is_aligned16(value) && (a.shards > 0 || is_aligned16(a.param)) && a.dst_aligned16;
   if (OP == UpdateOp::kAdam) aligned = aligned && is_aligned16(a.moment1) && is_aligned16(a.moment2);
@@ -598,8 +639,6 @@ cudaError_t launch_op(const SortedPlan& plan, const T* value, int64_t n, int64_t
       const size_t smem = sizeof(T) * 2 * GPC * COLS + sizeof(uint32_t) * 2 * GPC * chunk;
       k_chunk_reduce<T, OP, LPR, NV, VEC><<<ctas, kBlock, smem, s>>>(plan.keys, plan.perm, ni, chunk,
                                                                      value, P, C);
-      if (ctas > 1)
-        k_fixup<T, OP, LPR, NV, VEC><<<ctas, kBlock, sizeof(T) * GPC * COLS, s>>>(ctas, P, C);
     }
     err = cudaGetLastError();
   });

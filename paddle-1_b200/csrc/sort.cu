@@ -58,11 +58,13 @@ template <int BITS>
 __global__ void __launch_bounds__(kSortThreads, 4)
 k_prepare_direct(const int64_t* __restrict__ rows, int n, uint32_t height, KeyMap km, int passes,
                  uint32_t* __restrict__ keys, uint32_t* __restrict__ hmat, size_t per_pass,
-                 int32_t* status) {
+                 uint32_t* __restrict__ arrive, int arrive_n, int32_t* status) {
   constexpr int kBins = 1 << BITS;
   __shared__ uint32_t sh[kBins];
   const int tid = threadIdx.x, lane = tid & 31;
   const int tile = blockIdx.x;
+  // the chunked reduce's chain arrival counters (segreduce.cu) start every plan at zero
+  for (int i = tile * kSortThreads + tid; i < arrive_n; i += gridDim.x * kSortThreads) arrive[i] = 0;
   for (int i = tid; i < kBins; i += kSortThreads) sh[i] = 0;
   __syncthreads();
   bool bad = false;
@@ -426,9 +428,7 @@ Workspace make_workspace(int64_t n, int64_t d, int64_t elem_size) {
   for (int b = 0; b < 2; ++b) L.off_perm[b] = take(sizeof(uint32_t) * n);
   L.off_uidx = take(sizeof(uint32_t) * n);
   L.off_seg_start = take(sizeof(uint32_t) * (n + 1));
-  L.off_cta_flags = take(sizeof(uint32_t) * L.max_ctas);
-  L.off_cta_tail_key = take(sizeof(uint32_t) * L.max_ctas);
-  L.off_cta_tail_eref = take(sizeof(uint32_t) * L.max_ctas);
+  L.off_cta_arrive = take(sizeof(uint32_t) * L.max_ctas);
   L.off_cta_head = take(static_cast<size_t>(elem_size) * L.max_ctas * d);
   L.off_cta_tail = take(static_cast<size_t>(elem_size) * L.max_ctas * d);
   L.total = off;
@@ -455,8 +455,9 @@ cudaError_t launch_passes_direct(const int64_t* rows, int n, uint32_t height, Ke
   uint32_t* hmat = reinterpret_cast<uint32_t*>(ws + L.off_digit_counts);
   const int tiles = static_cast<int>(L.sort_tiles);
   const size_t per_pass = static_cast<size_t>(tiles + 1) * kBins;   // + the totals row
-  k_prepare_direct<BITS><<<tiles, kSortThreads, 0, s>>>(rows, n, height, km, passes, keys[0], hmat,
-                                                        per_pass, status);
+  k_prepare_direct<BITS><<<tiles, kSortThreads, 0, s>>>(
+      rows, n, height, km, passes, keys[0], hmat, per_pass,
+      reinterpret_cast<uint32_t*>(ws + L.off_cta_arrive), static_cast<int>(L.max_ctas), status);
   for (int p = 0; p < passes; ++p) {
     uint32_t* hn = p + 1 < passes ? hmat + (p + 1) * per_pass : nullptr;
     if constexpr (SCANNED)
@@ -490,6 +491,8 @@ cudaError_t launch_plan(const int64_t* rows, int64_t n, int64_t height, char* ws
     cudaError_t ce = launch_cluster_sort(
         rows, n, height, cpasses, reinterpret_cast<uint32_t*>(ws + L.off_keys[dp.passes & 1]),
         reinterpret_cast<uint32_t*>(ws + L.off_perm[dp.passes & 1]), status, s);
+    if (ce == cudaSuccess)
+      ce = cudaMemsetAsync(ws + L.off_cta_arrive, 0, sizeof(uint32_t) * L.max_ctas, s);
     if (ce == cudaSuccess) {
       if (out) *out = plan_view(n, height, ws, L);
       return cudaSuccess;
