@@ -20,6 +20,8 @@ The only host synchronisation per step is the read of the split sizes (G x (G+1)
 `ops` is the compute backend (CudaOps = the C-ABI kernels; tests inject a CPU checker backend to
 exercise this file's logic with gloo), `torch.distributed` is the communication backend.
 """
+import contextlib
+
 import torch
 import torch.distributed as dist
 
@@ -185,22 +187,61 @@ class ShardedTable:
         dist.all_reduce(self.sync_word, group=self.group)
 
     # ------------------------------------------------------------------ forward
-    def lookup(self, ids, ws, deterministic=False):
-        """ids: int64 [n] on this rank.  Returns (out [n, d], ctx for update())."""
-        n = ids.numel()
-        with self._phase("plan+dedup"):
-            ukeys, n_unique, bounds, ebounds, local = self.ops.plan_unique(ids, self.height, self.world, ws,
-                                                                           deterministic)
-        # split sizes of every rank in one collective + one host read
-        mine = bounds if ebounds is None else torch.cat([bounds, ebounds])
-        with self._phase("split sizes (all_gather + host read)"):
-            if self.world > 1:
-                gathered = [torch.empty_like(mine) for _ in range(self.world)]
-                dist.all_gather(gathered, mine, group=self.group)
-                table_d = torch.stack(gathered)
+    def prepare(self, ids, ws, deterministic=False, stream=None):
+        """The ids-only part of lookup(): sort plan + de-duplication in `ws`, the split sizes of every rank
+        (one all_gather) and their copy to the host.  Needs nothing but the ids, so a training loop can run
+        it for batch i+1 on a side `stream` while batch i is still in flight (a data-loader prefetch); the
+        host then finds the sizes already there instead of stalling the device queue on a mid-step read."""
+        cur = torch.cuda.current_stream(ids.device) if ids.is_cuda else None
+        use = stream if (stream is not None and ids.is_cuda) else None
+        if use is not None:
+            use.wait_stream(cur)             # ws / ids of this batch are free of earlier steps' work
+        with (torch.cuda.stream(use) if use is not None else contextlib.nullcontext()):
+            with self._phase("plan+dedup"):
+                ukeys, n_unique, bounds, ebounds, local = self.ops.plan_unique(ids, self.height, self.world, ws,
+                                                                               deterministic)
+            mine = bounds if ebounds is None else torch.cat([bounds, ebounds])
+            with self._phase("split sizes (all_gather)"):
+                if self.world > 1:
+                    gathered = [torch.empty_like(mine) for _ in range(self.world)]
+                    dist.all_gather(gathered, mine, group=self.group)
+                    table_d = torch.stack(gathered)
+                else:
+                    table_d = mine.reshape(1, -1)
+            event = None
+            if ids.is_cuda:
+                slot = self._host_slot = (getattr(self, "_host_slot", -1) + 1) % 4
+                if not hasattr(self, "_host_tables"):
+                    self._host_tables = [None] * 4
+                if self._host_tables[slot] is None or self._host_tables[slot].shape != table_d.shape:
+                    self._host_tables[slot] = torch.empty(table_d.shape, dtype=table_d.dtype).pin_memory()
+                table = self._host_tables[slot]
+                table.copy_(table_d, non_blocking=True)
+                event = torch.cuda.Event()
+                event.record()
             else:
-                table_d = mine.reshape(1, -1)
-            table = table_d.cpu()
+                table = table_d
+        if use is not None:
+            for t in (ukeys, n_unique, bounds, ebounds, local, table_d):
+                if t is not None:
+                    t.record_stream(cur)
+        return {"ids": ids, "ws": ws, "deterministic": deterministic, "bounds": bounds, "ebounds": ebounds,
+                "local": local, "table_d": table_d, "table": table, "event": event, "stream": use}
+
+    def lookup(self, ids, ws, deterministic=False, prep=None):
+        """ids: int64 [n] on this rank.  Returns (out [n, d], ctx for update()).  `prep` = the result of
+        prepare() on the same (ids, ws) if it was issued ahead of time."""
+        n = ids.numel()
+        if prep is None:
+            prep = self.prepare(ids, ws, deterministic)
+        assert prep["ids"] is ids and prep["ws"] is ws and prep["deterministic"] == deterministic
+        bounds, ebounds, local, table_d = prep["bounds"], prep["ebounds"], prep["local"], prep["table_d"]
+        with self._phase("split sizes (host read)"):
+            if prep["event"] is not None:
+                prep["event"].synchronize()
+                if prep["stream"] is not None:
+                    torch.cuda.current_stream(ids.device).wait_event(prep["event"])
+            table = prep["table"].clone() if prep["event"] is not None else prep["table"]
         g1 = self.world + 1
         ub = table[:, :g1]
         send = (ub[self.rank, 1:] - ub[self.rank, :-1]).tolist()

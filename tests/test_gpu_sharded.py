@@ -77,7 +77,10 @@ def test_sharded_table_world1_cuda(capi, pkg, deterministic):
     tab = pkg.sharded.ShardedTable(v, d, pkg.sharded.CudaOps(capi), torch.device("cuda"),
                                    init=lambda rows: torch.from_numpy(full[rows.numpy()]))
     ws = capi.alloc_workspace(n, d)
-    out, ctx = tab.lookup(torch.from_numpy(ids).cuda(), ws, deterministic=deterministic)
+    ids_d = torch.from_numpy(ids).cuda()
+    # the fast variant issues the ids-only part ahead of time on a side stream (the bench's prefetch)
+    prep = None if deterministic else tab.prepare(ids_d, ws, deterministic, stream=torch.cuda.Stream())
+    out, ctx = tab.lookup(ids_d, ws, deterministic=deterministic, prep=prep)
     assert np.array_equal(out.cpu().numpy(), full[ids])
     lr = torch.tensor([0.05], device="cuda")
     tab.update(ctx, torch.from_numpy(dout).cuda(), lr, deterministic=deterministic)
@@ -116,7 +119,9 @@ def _nccl_worker(rank, world, port, deterministic, q, peer=False):
         ws = pkg.capi.alloc_workspace(n, d, 4, dev)
         if peer:
             assert tab.enable_peer_exchange(n, 2 * n)
-        out, ctx = tab.lookup(torch.from_numpy(ids).to(dev), ws, deterministic=deterministic)
+        ids_d = torch.from_numpy(ids).to(dev)
+        prep = tab.prepare(ids_d, ws, deterministic, stream=torch.cuda.Stream(dev)) if peer else None
+        out, ctx = tab.lookup(ids_d, ws, deterministic=deterministic, prep=prep)
         ok = np.array_equal(out.cpu().numpy(), full[ids]) and (ctx["fused"] == (peer and not deterministic))
         tab.update(ctx, torch.from_numpy(dout).to(dev), torch.tensor([0.05], device=dev), deterministic=deterministic)
         after = tab.gather_full_table().cpu().numpy()
