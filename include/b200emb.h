@@ -53,6 +53,7 @@ extern "C" {
 
 #define B200EMB_STATUS_BAD_LOOKUP_ID 1
 #define B200EMB_STATUS_BAD_GRAD_ROW 2
+#define B200EMB_STATUS_BARRIER_TIMEOUT 4   /* b200emb_peer_barrier gave up waiting for a rank */
 
 int b200emb_abi_version(void);
 /* cudaError_t of the last failing CUDA call made by this library on the calling thread. */
@@ -214,6 +215,17 @@ int b200emb_peer_alloc(size_t bytes, void** ptr, unsigned char* handle64);
 int b200emb_peer_open(const unsigned char* handle64, void** ptr);
 int b200emb_peer_close(void* ptr);
 int b200emb_peer_free(void* ptr);
+
+/* Stream-ordered barrier across the ranks of the sharded path, over peer memory instead of a
+ * collective (no counterpart in the reference).  flag_ptrs: DEVICE array of `world` pointers, entry r
+ * = rank r's flag array (uint64[world], zeroed at set-up, peer-mapped like the buffers above).  One
+ * tiny kernel: thread r stores `epoch` (release, system scope) into slot [rank] of rank r's array,
+ * then waits (acquire) until slot [r] of this rank's own array reaches `epoch`.  `epoch` must grow by
+ * one per barrier on every rank.  Everything the preceding kernels of `stream` stored into peer
+ * buffers is visible to the kernels the peers launch after their own barrier.  A rank that does not
+ * show up within ~20 s raises B200EMB_STATUS_BARRIER_TIMEOUT in `status` instead of hanging. */
+int b200emb_peer_barrier(void* const* flag_ptrs, int world, int rank, uint64_t epoch,
+                         int32_t* status, void* stream);
 
 /* scatter::MergeAdd — replaces math/selected_rows_functor.cu:235-297 (CPU semantics
  * selected_rows_functor.cc:193-228): out_rows = ascending unique rows, out_value[u,:] = sum of

@@ -37,6 +37,7 @@ EXPORTS = [
     "b200emb_split_selected_rows_f32", "b200emb_split_selected_rows_f64", "b200emb_extract_rows",
     "b200emb_sparse_decay_f32", "b200emb_sparse_decay_f64",
     "b200emb_peer_alloc", "b200emb_peer_open", "b200emb_peer_close", "b200emb_peer_free",
+    "b200emb_peer_barrier",
 ]
 
 _lib = None
@@ -356,6 +357,13 @@ class PeerBuffer:
         if self.ptr:
             lib().b200emb_peer_free(ctypes.c_void_p(self.ptr))
             self.ptr = 0
+
+
+def peer_barrier(flag_ptrs, world, rank, epoch, status=None):
+    """Stream-ordered barrier over peer memory; flag_ptrs = device int64[world] of the ranks' flag arrays."""
+    _need_cuda(flag_ptrs, status)
+    _check(lib().b200emb_peer_barrier(_ptr(flag_ptrs), ctypes.c_int(world), ctypes.c_int(rank),
+                                      ctypes.c_uint64(epoch), _ptr(status), _stream()), "peer_barrier")
 
 
 def peer_open(handle_bytes):

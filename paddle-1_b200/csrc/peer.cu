@@ -4,9 +4,47 @@
 #include "../../include/b200emb.h"
 
 #include <cuda_runtime.h>
+#include <cstdint>
 #include <cstring>
 
+namespace {
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// one thread per rank: announce to it, then wait for it
+__global__ void k_peer_barrier(unsigned long long* const* __restrict__ flags, int world, int rank,
+                               unsigned long long epoch, int32_t* status) {
+  const int r = threadIdx.x;
+  if (r >= world) return;
+  unsigned long long* dst = flags[r] + rank;
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(dst), "l"(epoch) : "memory");
+  const unsigned long long* src = flags[rank] + r;
+  const unsigned long long t0 = global_ns();
+  unsigned long long v;
+  for (;;) {
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(src) : "memory");
+    if (v >= epoch) break;
+    if (global_ns() - t0 > 20000000000ull) {   // 20 s: a rank is gone; do not hang the device
+      if (status) atomicOr(status, B200EMB_STATUS_BARRIER_TIMEOUT);
+      break;
+    }
+    __nanosleep(64);
+  }
+}
+}  // namespace
+
 extern "C" {
+
+int b200emb_peer_barrier(void* const* flag_ptrs, int world, int rank, uint64_t epoch,
+                         int32_t* status, void* stream) {
+  if (!flag_ptrs || world < 1 || world > 1024 || rank < 0 || rank >= world) return B200EMB_E_INVALID;
+  k_peer_barrier<<<1, ((world + 31) / 32) * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<unsigned long long* const*>(flag_ptrs), world, rank, epoch, status);
+  return cudaGetLastError() == cudaSuccess ? B200EMB_OK : B200EMB_E_CUDA;
+}
 
 int b200emb_peer_alloc(size_t bytes, void** ptr, unsigned char* handle64) {
   if (!ptr || !handle64 || bytes == 0) return B200EMB_E_INVALID;

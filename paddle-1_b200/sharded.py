@@ -21,6 +21,7 @@ The only host synchronisation per step is the read of the split sizes (G x (G+1)
 exercise this file's logic with gloo), `torch.distributed` is the communication backend.
 """
 import contextlib
+import os
 
 import torch
 import torch.distributed as dist
@@ -161,19 +162,29 @@ class ShardedTable:
         self.peer_u = capi.PeerBuffer(self.cap_u * self.d * item)
         self.peer_g = capi.PeerBuffer(self.cap_r * self.d * item)
         self.peer_i = capi.PeerBuffer(self.cap_r * 8)
+        self.peer_f = capi.PeerBuffer(max(self.world * 8, 256))        # barrier flags: uint64[world]
+        self.peer_f.tensor((max(self.world, 32),), torch.int64).zero_()
+        torch.cuda.synchronize(self.device)
         handles = [None] * self.world
-        dist.all_gather_object(handles, (self.peer_u.handle, self.peer_g.handle, self.peer_i.handle),
-                               group=self.group)
-        self.peer_u_ptr, self.peer_g_ptr, self.peer_i_ptr = [], [], []
-        for r, (hu, hg, hi) in enumerate(handles):
+        dist.all_gather_object(handles, (self.peer_u.handle, self.peer_g.handle, self.peer_i.handle,
+                                         self.peer_f.handle), group=self.group)
+        self.peer_u_ptr, self.peer_g_ptr, self.peer_i_ptr, peer_f_ptr = [], [], [], []
+        for r, (hu, hg, hi, hf) in enumerate(handles):
             if r == self.rank:
                 self.peer_u_ptr.append(self.peer_u.ptr)
                 self.peer_g_ptr.append(self.peer_g.ptr)
                 self.peer_i_ptr.append(self.peer_i.ptr)
+                peer_f_ptr.append(self.peer_f.ptr)
             else:
                 self.peer_u_ptr.append(capi.peer_open(hu))
                 self.peer_g_ptr.append(capi.peer_open(hg))
                 self.peer_i_ptr.append(capi.peer_open(hi))
+                peer_f_ptr.append(capi.peer_open(hf))
+        self.peer_f_ptr_t = torch.tensor(peer_f_ptr, dtype=torch.int64, device=self.device)
+        self.barrier_epoch = 0
+        self.barrier_status = torch.zeros(1, dtype=torch.int32, device=self.device)
+        # collective fallback (A/B switch): a 4-byte all_reduce
+        self.nccl_barrier = os.environ.get("B200EMB_NCCL_BARRIER") is not None
         self.peer_i_ptr_t = torch.tensor(self.peer_i_ptr, dtype=torch.int64, device=self.device)
         self.peer_u_ptr_t = torch.tensor(self.peer_u_ptr, dtype=torch.int64, device=self.device)
         self.peer_g_ptr_t = torch.tensor(self.peer_g_ptr, dtype=torch.int64, device=self.device)
@@ -184,7 +195,12 @@ class ShardedTable:
 
     def _device_barrier(self):
         # stream-ordered cross-GPU barrier: every rank's preceding kernels (peer stores) have completed
-        dist.all_reduce(self.sync_word, group=self.group)
+        if self.nccl_barrier:
+            dist.all_reduce(self.sync_word, group=self.group)
+            return
+        self.barrier_epoch += 1
+        self.ops.capi.peer_barrier(self.peer_f_ptr_t, self.world, self.rank, self.barrier_epoch,
+                                   self.barrier_status)
 
     # ------------------------------------------------------------------ forward
     def prepare(self, ids, ws, deterministic=False, stream=None):

@@ -125,6 +125,8 @@ def _nccl_worker(rank, world, port, deterministic, q, peer=False):
         ok = np.array_equal(out.cpu().numpy(), full[ids]) and (ctx["fused"] == (peer and not deterministic))
         tab.update(ctx, torch.from_numpy(dout).to(dev), torch.tensor([0.05], device=dev), deterministic=deterministic)
         after = tab.gather_full_table().cpu().numpy()
+        if peer:   # the peer-memory barriers all completed (no time-out bit)
+            ok = ok and tab.barrier_epoch >= 3 and int(tab.barrier_status.item()) == 0
         q.put((rank, ok, after if rank == 0 else None, ids, dout))
     finally:
         dist.destroy_process_group()
