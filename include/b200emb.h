@@ -227,6 +227,21 @@ int b200emb_peer_free(void* ptr);
 int b200emb_peer_barrier(void* const* flag_ptrs, int world, int rank, uint64_t epoch,
                          int32_t* status, void* stream);
 
+/* Scatter maps of the fused exchange, one tiny kernel instead of a dozen tensor ops on the step path.
+ * split_table: device int64 [world][cols], row r = rank r's shard_bounds (b200emb_plan_unique_rows),
+ * all-gathered; peer_*_ptrs: device int64[world] = every rank's id / unique-row / gradient receive buffer.
+ * With before[g] = sum over ranks r < rank of (split_table[r][g+1] - split_table[r][g]) (this rank's slot in
+ * owner g's buffers: ranks before it come first, the reference's gather-concat order) and
+ * cnt[r] = split_table[r][rank+1] - split_table[r][rank] (rows rank r requests from this owner):
+ *   out[0][g] = peer_i_ptrs[g] + 8*before[g]                    id destinations (segment_scatter_i64)
+ *   out[1][r] = cnt[0] + ... + cnt[r-1],  r = 0..world          owner-gather segment starts
+ *   out[2][r] = peer_u_ptrs[r] + row_bytes*split_table[r][rank]  owner-gather destinations
+ *   out[3][g] = peer_g_ptrs[g] + row_bytes*before[g]             merged-gradient destinations
+ * out: device int64 [4][world+1]. */
+int b200emb_exchange_maps(const int64_t* split_table, int world, int cols, int rank,
+                          const int64_t* peer_i_ptrs, const int64_t* peer_u_ptrs,
+                          const int64_t* peer_g_ptrs, int64_t row_bytes, int64_t* out, void* stream);
+
 /* scatter::MergeAdd — replaces math/selected_rows_functor.cu:235-297 (CPU semantics
  * selected_rows_functor.cc:193-228): out_rows = ascending unique rows, out_value[u,:] = sum of
  * the input rows with that id.  out_rows/out_value must hold n rows; *n_unique (device int64)

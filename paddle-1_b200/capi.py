@@ -37,7 +37,7 @@ EXPORTS = [
     "b200emb_split_selected_rows_f32", "b200emb_split_selected_rows_f64", "b200emb_extract_rows",
     "b200emb_sparse_decay_f32", "b200emb_sparse_decay_f64",
     "b200emb_peer_alloc", "b200emb_peer_open", "b200emb_peer_close", "b200emb_peer_free",
-    "b200emb_peer_barrier",
+    "b200emb_peer_barrier", "b200emb_exchange_maps",
 ]
 
 _lib = None
@@ -73,7 +73,9 @@ def _ptr(t):
 
 
 def _stream():
-    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    # the raw handle of torch's current stream; torch.cuda.current_stream() builds a Stream object and
+    # costs ~15 us per call, which adds up over the ~20 launches of a sharded step
+    return ctypes.c_void_p(torch._C._cuda_getCurrentRawStream(torch._C._cuda_getDevice()))
 
 
 def _sfx(dtype):
@@ -342,16 +344,19 @@ class PeerBuffer:
         n = 1
         for x in shape:
             n *= int(x)
-        item = torch.empty(0, dtype=dtype).element_size()
-        assert n * item <= self.nbytes
-        typestr = {torch.float32: "<f4", torch.float64: "<f8", torch.int64: "<i8", torch.uint8: "|u1"}[dtype]
+        base = self.opened.get(dtype)
+        if base is None:          # one full-size view per dtype, sliced per call
+            item = torch.empty(0, dtype=dtype).element_size()
+            typestr = {torch.float32: "<f4", torch.float64: "<f8", torch.int64: "<i8", torch.uint8: "|u1"}[dtype]
 
-        class _Iface:
-            pass
-        o = _Iface()
-        o.__cuda_array_interface__ = {"shape": tuple(int(x) for x in shape), "typestr": typestr,
-                                      "data": (self.ptr, False), "version": 2}
-        return torch.as_tensor(o, device="cuda")
+            class _Iface:
+                pass
+            o = _Iface()
+            o.__cuda_array_interface__ = {"shape": (self.nbytes // item,), "typestr": typestr,
+                                          "data": (self.ptr, False), "version": 2}
+            base = self.opened[dtype] = torch.as_tensor(o, device="cuda")
+        assert n <= base.numel()
+        return base[:n].view(tuple(int(x) for x in shape))
 
     def free(self):
         if self.ptr:
@@ -364,6 +369,20 @@ def peer_barrier(flag_ptrs, world, rank, epoch, status=None):
     _need_cuda(flag_ptrs, status)
     _check(lib().b200emb_peer_barrier(_ptr(flag_ptrs), ctypes.c_int(world), ctypes.c_int(rank),
                                       ctypes.c_uint64(epoch), _ptr(status), _stream()), "peer_barrier")
+
+
+def exchange_maps(split_table, rank, peer_i_ptrs, peer_u_ptrs, peer_g_ptrs, row_bytes, out=None):
+    """Scatter maps of the fused exchange from the all-gathered split table (device int64 [world, >=world+1]):
+    out[0,:world] id destinations, out[1,:world+1] owner-gather segment starts, out[2,:world] owner-gather
+    destinations, out[3,:world] gradient destinations (see b200emb_exchange_maps)."""
+    _need_cuda(split_table, peer_i_ptrs, peer_u_ptrs, peer_g_ptrs, out)
+    world, cols = split_table.shape
+    if out is None:
+        out = torch.empty((4, world + 1), dtype=torch.int64, device=split_table.device)
+    _check(lib().b200emb_exchange_maps(_ptr(split_table), ctypes.c_int(world), ctypes.c_int(cols), ctypes.c_int(rank),
+                                       _ptr(peer_i_ptrs), _ptr(peer_u_ptrs), _ptr(peer_g_ptrs),
+                                       ctypes.c_int64(row_bytes), _ptr(out), _stream()), "exchange_maps")
+    return out
 
 
 def peer_open(handle_bytes):

@@ -34,9 +34,39 @@ __global__ void k_peer_barrier(unsigned long long* const* __restrict__ flags, in
     __nanosleep(64);
   }
 }
+// one thread per rank / owner; world <= 1024
+__global__ void k_exchange_maps(const int64_t* __restrict__ tab, int world, int cols, int rank,
+                                const int64_t* __restrict__ pi, const int64_t* __restrict__ pu,
+                                const int64_t* __restrict__ pg, int64_t row_bytes, int64_t* __restrict__ out) {
+  const int g = threadIdx.x;
+  const int w1 = world + 1;
+  if (g < world) {
+    int64_t before = 0;
+    for (int r = 0; r < rank; ++r) before += tab[r * cols + g + 1] - tab[r * cols + g];
+    out[0 * w1 + g] = pi[g] + 8 * before;
+    out[3 * w1 + g] = pg[g] + row_bytes * before;
+    out[2 * w1 + g] = pu[g] + row_bytes * tab[g * cols + rank];
+  }
+  if (g <= world) {
+    int64_t start = 0;
+    for (int r = 0; r < g; ++r) start += tab[r * cols + rank + 1] - tab[r * cols + rank];
+    out[1 * w1 + g] = start;
+  }
+}
 }  // namespace
 
 extern "C" {
+
+int b200emb_exchange_maps(const int64_t* split_table, int world, int cols, int rank,
+                          const int64_t* peer_i_ptrs, const int64_t* peer_u_ptrs,
+                          const int64_t* peer_g_ptrs, int64_t row_bytes, int64_t* out, void* stream) {
+  if (!split_table || !peer_i_ptrs || !peer_u_ptrs || !peer_g_ptrs || !out || world < 1 || world > 1023 ||
+      cols < world + 1 || rank < 0 || rank >= world)
+    return B200EMB_E_INVALID;
+  k_exchange_maps<<<1, ((world + 1 + 31) / 32) * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+      split_table, world, cols, rank, peer_i_ptrs, peer_u_ptrs, peer_g_ptrs, row_bytes, out);
+  return cudaGetLastError() == cudaSuccess ? B200EMB_OK : B200EMB_E_CUDA;
+}
 
 int b200emb_peer_barrier(void* const* flag_ptrs, int world, int rank, uint64_t epoch,
                          int32_t* status, void* stream) {

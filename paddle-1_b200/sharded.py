@@ -68,12 +68,13 @@ class CudaOps:
         self.capi.merge_add_scatter(ids, value, plan_h, shard_bounds, shard_dst, ws,
                                     flags=self.capi.PLAN_READY | self.capi.UNIQUE_READY)
 
-    def sgd(self, shard, rows, grads, lr, deterministic, ws=None):
-        flags = self.capi.DETERMINISTIC if deterministic else 0
+    def sgd(self, shard, rows, grads, lr, deterministic, ws=None, plan_ready=False):
+        flags = (self.capi.DETERMINISTIC if deterministic else 0) | (self.capi.PLAN_READY if plan_ready else 0)
         self.capi.sparse_sgd(shard, rows, grads, lr, workspace=ws, flags=flags)
 
-    def adam(self, shard, m1, m2, rows, grads, lr, b1p, b2p, beta1, beta2, eps, deterministic, ws=None):
-        flags = self.capi.DETERMINISTIC if deterministic else 0
+    def adam(self, shard, m1, m2, rows, grads, lr, b1p, b2p, beta1, beta2, eps, deterministic, ws=None,
+             plan_ready=False):
+        flags = (self.capi.DETERMINISTIC if deterministic else 0) | (self.capi.PLAN_READY if plan_ready else 0)
         self.capi.sparse_adam(shard, m1, m2, rows, grads, lr, b1p, b2p, beta1, beta2, eps, workspace=ws,
                               flags=flags)
 
@@ -219,11 +220,18 @@ class ShardedTable:
             mine = bounds if ebounds is None else torch.cat([bounds, ebounds])
             with self._phase("split sizes (all_gather)"):
                 if self.world > 1:
-                    gathered = [torch.empty_like(mine) for _ in range(self.world)]
-                    dist.all_gather(gathered, mine, group=self.group)
-                    table_d = torch.stack(gathered)
+                    flat = torch.empty(self.world * mine.numel(), dtype=mine.dtype, device=mine.device)
+                    dist.all_gather_into_tensor(flat, mine, group=self.group)
+                    table_d = flat.view(self.world, mine.numel())
                 else:
                     table_d = mine.reshape(1, -1)
+            maps = None
+            if self.peer and ids.is_cuda:
+                # scatter maps of the fused exchange, computed on the device from the gathered split table
+                m = self.ops.capi.exchange_maps(table_d, self.rank, self.peer_i_ptr_t, self.peer_u_ptr_t,
+                                                self.peer_g_ptr_t, self.row_bytes)
+                w = self.world
+                maps = {"all": m, "id_dst": m[0, :w], "seg_start": m[1], "seg_dst": m[2, :w], "shard_dst": m[3, :w]}
             event = None
             if ids.is_cuda:
                 slot = self._host_slot = (getattr(self, "_host_slot", -1) + 1) % 4
@@ -238,15 +246,17 @@ class ShardedTable:
             else:
                 table = table_d
         if use is not None:
-            for t in (ukeys, n_unique, bounds, ebounds, local, table_d):
+            for t in (ukeys, n_unique, bounds, ebounds, local, table_d, maps["all"] if maps else None):
                 if t is not None:
                     t.record_stream(cur)
         return {"ids": ids, "ws": ws, "deterministic": deterministic, "bounds": bounds, "ebounds": ebounds,
-                "local": local, "table_d": table_d, "table": table, "event": event, "stream": use}
+                "local": local, "table_d": table_d, "table": table, "event": event, "stream": use, "maps": maps}
 
-    def lookup(self, ids, ws, deterministic=False, prep=None):
+    def lookup(self, ids, ws, deterministic=False, prep=None, owner_ws=None, owner_stream=None):
         """ids: int64 [n] on this rank.  Returns (out [n, d], ctx for update()).  `prep` = the result of
-        prepare() on the same (ids, ws) if it was issued ahead of time."""
+        prepare() on the same (ids, ws) if it was issued ahead of time.  With `owner_ws` (the workspace
+        update() will get) the owner-side sort plan of the received row ids is built right after the id
+        exchange — on `owner_stream` if given — instead of on update()'s critical path."""
         n = ids.numel()
         if prep is None:
             prep = self.prepare(ids, ws, deterministic)
@@ -257,35 +267,46 @@ class ShardedTable:
                 prep["event"].synchronize()
                 if prep["stream"] is not None:
                     torch.cuda.current_stream(ids.device).wait_event(prep["event"])
-            table = prep["table"].clone() if prep["event"] is not None else prep["table"]
+            table = prep["table"].numpy().copy()      # G x (G+1) integers (numpy: cheaper than tensor ops here)
         g1 = self.world + 1
         ub = table[:, :g1]
         send = (ub[self.rank, 1:] - ub[self.rank, :-1]).tolist()
         recv = (ub[:, self.rank + 1] - ub[:, self.rank]).tolist()
         u = int(ub[self.rank, self.world])
         fused = (self.peer and not deterministic and int(ub[:, self.world].max()) <= self.cap_u and
-                 int((ub[:, 1:] - ub[:, :-1]).sum(dim=0).max()) <= self.cap_r)
+                 int((ub[:, 1:] - ub[:, :-1]).sum(axis=0).max()) <= self.cap_r)
         if fused:
-            ubd = table_d[:, :g1]
-            # rows of lower ranks per owner = this rank's slot in each owner's receive buffers
-            before_me = (ubd[: self.rank, 1:] - ubd[: self.rank, :-1]).sum(dim=0)
+            maps = prep["maps"]
             with self._phase("id scatter to owners (peer stores)"):
-                self.ops.ids_scatter(local, n, bounds, self.peer_i_ptr_t + before_me * 8)
+                self.ops.ids_scatter(local, n, bounds, maps["id_dst"])
             with self._phase("barrier"):
                 self._device_barrier()
-            recv_local = self.peer_i.tensor((sum(recv),), torch.int64)
+            # private copy: a faster peer may start the NEXT step's id scatter into peer_i while this rank's
+            # owner update still needs these ids (nothing between the two orders them)
+            recv_local = self.peer_i.tensor((sum(recv),), torch.int64).clone()
         else:
             recv_local = torch.empty(sum(recv), dtype=torch.int64, device=ids.device)
             with self._phase("id all-to-all"):
                 all_to_all_rows(recv_local, local[:u], recv, send, self.group)
+        # the owner-side plan of the rows this rank will update needs their ids only: start it now
+        owner_plan = None
+        if (owner_ws is not None and not deterministic and recv_local.numel() > 0 and recv_local.is_cuda and
+                owner_ws.numel() >= self.ops.capi.workspace_bytes(recv_local.numel(), self.d,
+                                                                  self.shard.element_size())):
+            cur = torch.cuda.current_stream(ids.device)
+            if owner_stream is not None:
+                owner_stream.wait_stream(cur)
+            with (torch.cuda.stream(owner_stream) if owner_stream is not None else contextlib.nullcontext()):
+                with self._phase("owner sort plan (ids only)"):
+                    self.ops.capi.plan_rows(recv_local, self.hs, owner_ws)
+                owner_plan = torch.cuda.Event()
+                owner_plan.record()
+            if owner_stream is not None:
+                recv_local.record_stream(owner_stream)
         if fused:
             # owner side: gather from the shard straight into every requester's unique-row buffer
-            # scatter maps computed on the device from the gathered split table (no host round trip)
-            seg_start = torch.zeros(g1, dtype=torch.int64, device=ids.device)
-            seg_start[1:] = torch.cumsum(ubd[:, self.rank + 1] - ubd[:, self.rank], dim=0)
-            seg_dst = self.peer_u_ptr_t + ubd[:, self.rank] * self.row_bytes
             with self._phase("owner gather + peer stores (fused row exchange)"):
-                self.ops.lookup_scatter(self.shard, recv_local, seg_start, seg_dst)
+                self.ops.lookup_scatter(self.shard, recv_local, maps["seg_start"], maps["seg_dst"])
             with self._phase("barrier"):
                 self._device_barrier()
             uvals = self.peer_u.tensor((u, self.d), self.dtype)
@@ -300,7 +321,8 @@ class ShardedTable:
             out = self.ops.expand_unique(uvals, n, self.plan_h, ws)
         self.bytes_sent += (u - send[self.rank]) * 8 + (sum(recv) - recv[self.rank]) * self.d * rows.element_size()
         ctx = {"ids": ids, "n": n, "u": u, "send": send, "recv": recv, "recv_local": recv_local, "ws": ws,
-               "fused": fused, "bounds": bounds, "ub": ub, "before_me": before_me if fused else None}
+               "fused": fused, "bounds": bounds, "ub": ub, "maps": prep["maps"] if fused else None,
+               "owner_plan": owner_plan, "owner_ws": owner_ws}
         if ebounds is not None:
             eb = table[:, g1:]
             ctx["esend"] = (eb[self.rank, 1:] - eb[self.rank, :-1]).tolist()
@@ -313,9 +335,8 @@ class ShardedTable:
         if not deterministic and ctx.get("fused"):
             # requester side: the local duplicate reduction stores every merged row straight into its owner's
             # receive buffer, at this rank's slot (ranks before it come first: reference gather-concat order)
-            shard_dst = self.peer_g_ptr_t + ctx["before_me"] * self.row_bytes
             with self._phase("local MergeAdd + peer stores (fused grad exchange)"):
-                self.ops.merge_scatter(ids, d_out, self.plan_h, ctx["bounds"], shard_dst, ws)
+                self.ops.merge_scatter(ids, d_out, self.plan_h, ctx["bounds"], ctx["maps"]["shard_dst"], ws)
             with self._phase("barrier"):
                 self._device_barrier()
             rows = ctx["recv_local"]
@@ -343,13 +364,17 @@ class ShardedTable:
             all_to_all_rows(grads, sorted_grads[:nvalid], erecv, esend, self.group)
         if rows.numel() == 0:
             return
+        extra = {}
+        if ctx.get("owner_plan") is not None and owner_ws is ctx.get("owner_ws") and rows is ctx["recv_local"]:
+            torch.cuda.current_stream(d_out.device).wait_event(ctx["owner_plan"])
+            extra = {"plan_ready": True}          # lookup() already sorted these row ids into owner_ws
         with self._phase("owner fused update"):
             if self.optimizer == "adam":
                 b1p, b2p, beta1, beta2, eps = adam_state
                 self.ops.adam(self.shard, self.m1, self.m2, rows, grads, lr, b1p, b2p, beta1, beta2, eps,
-                              deterministic, owner_ws)
+                              deterministic, owner_ws, **extra)
             else:
-                self.ops.sgd(self.shard, rows, grads, lr, deterministic, owner_ws)
+                self.ops.sgd(self.shard, rows, grads, lr, deterministic, owner_ws, **extra)
 
     def gather_full_table(self):
         """Debug/parity helper: the full [height, d] table on every rank (interleaved shards)."""

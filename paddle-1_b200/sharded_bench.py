@@ -55,13 +55,15 @@ def run(args):
     # side stream BEFORE the main-stream work of batch i is queued — the prefetch a data loader gives for
     # free — so the host finds the sizes of the next batch already copied and never stalls the device queue.
     side = torch.cuda.Stream(dev)
+    side2 = torch.cuda.Stream(dev)
     prefetch = os.environ.get("B200EMB_NO_PREFETCH") is None
 
     def step(b, prep=None, next_b=None, ids_b=None, dout_b=None):
         i = ids[b] if ids_b is None else ids_b
         g_ = dout[b] if dout_b is None else dout_b
         nxt = tab.prepare(ids[next_b], ws[next_b], stream=side) if (prefetch and next_b is not None) else None
-        out, ctx = tab.lookup(i, ws[b], prep=prep)
+        out, ctx = tab.lookup(i, ws[b], prep=prep, owner_ws=state["owner_ws"] if prefetch else None,
+                              owner_stream=side2)
         need = sum(ctx["recv"])
         if need > state["cap"]:
             state["cap"] = 2 * need
@@ -87,7 +89,15 @@ def run(args):
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    run_steps(args.steps)
+    if os.environ.get("B200EMB_PROFILE_HOST") and rank == 0:      # developer switch: where the host time goes
+        import cProfile, pstats, sys
+        pr = cProfile.Profile()
+        pr.enable()
+        run_steps(args.steps)
+        pr.disable()
+        pstats.Stats(pr, stream=sys.stderr).sort_stats("tottime").print_stats(28)
+    else:
+        run_steps(args.steps)
     e1.record()
     torch.cuda.synchronize()
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev)

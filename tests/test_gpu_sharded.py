@@ -121,9 +121,13 @@ def _nccl_worker(rank, world, port, deterministic, q, peer=False):
             assert tab.enable_peer_exchange(n, 2 * n)
         ids_d = torch.from_numpy(ids).to(dev)
         prep = tab.prepare(ids_d, ws, deterministic, stream=torch.cuda.Stream(dev)) if peer else None
-        out, ctx = tab.lookup(ids_d, ws, deterministic=deterministic, prep=prep)
+        ows = pkg.capi.alloc_workspace_upto(2 * n, d, 4, dev) if peer else None     # early owner-side plan
+        out, ctx = tab.lookup(ids_d, ws, deterministic=deterministic, prep=prep, owner_ws=ows,
+                              owner_stream=torch.cuda.Stream(dev) if peer else None)
         ok = np.array_equal(out.cpu().numpy(), full[ids]) and (ctx["fused"] == (peer and not deterministic))
-        tab.update(ctx, torch.from_numpy(dout).to(dev), torch.tensor([0.05], device=dev), deterministic=deterministic)
+        tab.update(ctx, torch.from_numpy(dout).to(dev), torch.tensor([0.05], device=dev), deterministic=deterministic,
+                   owner_ws=ows)
+        ok = ok and ((ctx["owner_plan"] is not None) == peer)
         after = tab.gather_full_table().cpu().numpy()
         if peer:   # the peer-memory barriers all completed (no time-out bit)
             ok = ok and tab.barrier_epoch >= 3 and int(tab.barrier_status.item()) == 0
