@@ -227,6 +227,17 @@ int b200emb_peer_free(void* ptr);
 int b200emb_peer_barrier(void* const* flag_ptrs, int world, int rank, uint64_t epoch,
                          int32_t* status, void* stream);
 
+/* All-gather of one small int64 row per rank (the split sizes of a step) over peer memory, barrier
+ * included — the collective-free counterpart of the all_gather the sharded path needs once per step.
+ * table_ptrs: DEVICE array of `world` pointers, entry r = rank r's table (int64[world][cols], peer-mapped);
+ * flag_ptrs as in b200emb_peer_barrier but a flag array of its own (uint64[world], zeroed at set-up);
+ * local_table = this rank's own table (= entry `rank`).  Thread r stores `row` into slot [rank] of rank r's
+ * table, publishes `epoch`, waits for rank r's; then, if host_copy != NULL (pinned host memory,
+ * world*cols int64), the complete local table is copied to the host on the same stream. */
+int b200emb_peer_allgather_i64(const int64_t* row, int cols, void* const* table_ptrs,
+                               const int64_t* local_table, void* const* flag_ptrs, int world, int rank,
+                               uint64_t epoch, int64_t* host_copy, int32_t* status, void* stream);
+
 /* Scatter maps of the fused exchange, one tiny kernel instead of a dozen tensor ops on the step path.
  * split_table: device int64 [world][cols], row r = rank r's shard_bounds (b200emb_plan_unique_rows),
  * all-gathered; peer_*_ptrs: device int64[world] = every rank's id / unique-row / gradient receive buffer.

@@ -37,7 +37,7 @@ EXPORTS = [
     "b200emb_split_selected_rows_f32", "b200emb_split_selected_rows_f64", "b200emb_extract_rows",
     "b200emb_sparse_decay_f32", "b200emb_sparse_decay_f64",
     "b200emb_peer_alloc", "b200emb_peer_open", "b200emb_peer_close", "b200emb_peer_free",
-    "b200emb_peer_barrier", "b200emb_exchange_maps",
+    "b200emb_peer_barrier", "b200emb_exchange_maps", "b200emb_peer_allgather_i64",
 ]
 
 _lib = None
@@ -72,9 +72,11 @@ def _ptr(t):
     return ctypes.c_void_p(0 if t is None else t.data_ptr())
 
 
-def _stream():
+def _stream(stream=None):
     # the raw handle of torch's current stream; torch.cuda.current_stream() builds a Stream object and
     # costs ~15 us per call, which adds up over the ~20 launches of a sharded step
+    if stream is not None:
+        return ctypes.c_void_p(stream if isinstance(stream, int) else stream.cuda_stream)
     return ctypes.c_void_p(torch._C._cuda_getCurrentRawStream(torch._C._cuda_getDevice()))
 
 
@@ -183,19 +185,19 @@ def sum_selected_rows(inputs):
     return out_rows, out_value
 
 
-def plan_rows(rows, height, workspace, status=None, unique=False):
+def plan_rows(rows, height, workspace, status=None, unique=False, stream=None):
     """Sort plan of `rows` into the workspace.  unique=True also leaves the unique index there
     (plan_unique_rows with one shard and no outputs): consumers then take PLAN_READY | UNIQUE_READY."""
     _need_cuda(rows, workspace, status)
     if unique:
         _check(lib().b200emb_plan_unique_rows(
             _ptr(rows), ctypes.c_int64(rows.numel()), ctypes.c_int64(height), ctypes.c_int64(1), None, None,
-            None, None, None, _ptr(workspace), ctypes.c_size_t(workspace.numel()), _ptr(status), _stream()),
-            "plan_unique_rows")
+            None, None, None, _ptr(workspace), ctypes.c_size_t(workspace.numel()), _ptr(status),
+            _stream(stream)), "plan_unique_rows")
         return
     _check(lib().b200emb_plan_rows(_ptr(rows), ctypes.c_int64(rows.numel()), ctypes.c_int64(height),
                                    _ptr(workspace), ctypes.c_size_t(workspace.numel()), _ptr(status),
-                                   _stream()), "plan_rows")
+                                   _stream(stream)), "plan_rows")
 
 
 def merge_add(rows, value, height, workspace=None, flags=0, status=None):
@@ -282,23 +284,31 @@ def plan_height(height, num_shards):
     return int(num_shards) * ((int(height) + num_shards - 1) // num_shards)
 
 
-def plan_unique_rows(rows, height, num_shards, workspace, status=None, want_elem_bounds=False):
+def plan_unique_rows(rows, height, num_shards, workspace, status=None, want_elem_bounds=False, out=None,
+                     stream=None):
     """Sort rows by (owner = id % num_shards, local row = id // num_shards) and de-duplicate.
 
     Returns (unique_keys[n], n_unique[1], shard_bounds[num_shards+1], elem_bounds or None, local_rows[n]);
-    only the first U entries of unique_keys / local_rows are meaningful.  The workspace keeps the plan."""
+    only the first U entries of unique_keys / local_rows are meaningful.  The workspace keeps the plan.
+    `out` = the same five tensors preallocated by the caller (elem_bounds may be None); `stream` = the
+    stream to launch on (default: torch's current stream)."""
     _need_cuda(rows, workspace, status)
     n = rows.numel()
-    dev = rows.device
-    ukeys = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
-    local = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
-    n_unique = torch.zeros(1, dtype=torch.int64, device=dev)
-    bounds = torch.zeros(num_shards + 1, dtype=torch.int64, device=dev)
-    ebounds = torch.zeros(num_shards + 1, dtype=torch.int64, device=dev) if want_elem_bounds else None
+    if out is None:
+        dev = rows.device
+        ukeys = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
+        local = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
+        n_unique = torch.zeros(1, dtype=torch.int64, device=dev)
+        bounds = torch.zeros(num_shards + 1, dtype=torch.int64, device=dev)
+        ebounds = torch.zeros(num_shards + 1, dtype=torch.int64, device=dev) if want_elem_bounds else None
+    else:
+        ukeys, n_unique, bounds, ebounds, local = out
+        if not want_elem_bounds:
+            ebounds = None
     _check(lib().b200emb_plan_unique_rows(
         _ptr(rows), ctypes.c_int64(n), ctypes.c_int64(height), ctypes.c_int64(num_shards), _ptr(ukeys),
         _ptr(n_unique), _ptr(bounds), _ptr(ebounds), _ptr(local), _ptr(workspace),
-        ctypes.c_size_t(workspace.numel()), _ptr(status), _stream()), "plan_unique_rows")
+        ctypes.c_size_t(workspace.numel()), _ptr(status), _stream(stream)), "plan_unique_rows")
     return ukeys, n_unique, bounds, ebounds, local
 
 
@@ -371,7 +381,17 @@ def peer_barrier(flag_ptrs, world, rank, epoch, status=None):
                                       ctypes.c_uint64(epoch), _ptr(status), _stream()), "peer_barrier")
 
 
-def exchange_maps(split_table, rank, peer_i_ptrs, peer_u_ptrs, peer_g_ptrs, row_bytes, out=None):
+def peer_allgather_i64(row, table_ptrs, local_table, flag_ptrs, world, rank, epoch, host_copy=None,
+                       status=None, stream=None):
+    """All-gather of one int64 row per rank over peer memory (see b200emb_peer_allgather_i64); `host_copy` = a
+    pinned host int64 tensor of world*row.numel() elements that receives the complete table."""
+    _check(lib().b200emb_peer_allgather_i64(
+        _ptr(row), ctypes.c_int(row.numel()), _ptr(table_ptrs), _ptr(local_table), _ptr(flag_ptrs),
+        ctypes.c_int(world), ctypes.c_int(rank), ctypes.c_uint64(epoch), _ptr(host_copy), _ptr(status),
+        _stream(stream)), "peer_allgather_i64")
+
+
+def exchange_maps(split_table, rank, peer_i_ptrs, peer_u_ptrs, peer_g_ptrs, row_bytes, out=None, stream=None):
     """Scatter maps of the fused exchange from the all-gathered split table (device int64 [world, >=world+1]):
     out[0,:world] id destinations, out[1,:world+1] owner-gather segment starts, out[2,:world] owner-gather
     destinations, out[3,:world] gradient destinations (see b200emb_exchange_maps)."""
@@ -381,7 +401,7 @@ def exchange_maps(split_table, rank, peer_i_ptrs, peer_u_ptrs, peer_g_ptrs, row_
         out = torch.empty((4, world + 1), dtype=torch.int64, device=split_table.device)
     _check(lib().b200emb_exchange_maps(_ptr(split_table), ctypes.c_int(world), ctypes.c_int(cols), ctypes.c_int(rank),
                                        _ptr(peer_i_ptrs), _ptr(peer_u_ptrs), _ptr(peer_g_ptrs),
-                                       ctypes.c_int64(row_bytes), _ptr(out), _stream()), "exchange_maps")
+                                       ctypes.c_int64(row_bytes), _ptr(out), _stream(stream)), "exchange_maps")
     return out
 
 

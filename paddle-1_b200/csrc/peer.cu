@@ -34,6 +34,31 @@ __global__ void k_peer_barrier(unsigned long long* const* __restrict__ flags, in
     __nanosleep(64);
   }
 }
+// all-gather of one small int64 row per rank over peer memory, with its own barrier: thread r stores this
+// rank's row into slot [rank] of rank r's table, publishes `epoch` in rank r's flag array (release), then
+// waits for rank r's flag in the local array (acquire) — after the kernel the local table holds every row.
+__global__ void k_peer_allgather(const int64_t* __restrict__ row, int cols, int64_t* const* __restrict__ tables,
+                                 unsigned long long* const* __restrict__ flags, int world, int rank,
+                                 unsigned long long epoch, int32_t* status) {
+  const int r = threadIdx.x;
+  if (r >= world) return;
+  int64_t* dst = tables[r] + static_cast<size_t>(rank) * cols;
+  for (int c = 0; c < cols; ++c) dst[c] = row[c];
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(flags[r] + rank), "l"(epoch) : "memory");
+  const unsigned long long* src = flags[rank] + r;
+  const unsigned long long t0 = global_ns();
+  unsigned long long v;
+  for (;;) {
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(src) : "memory");
+    if (v >= epoch) break;
+    if (global_ns() - t0 > 20000000000ull) {
+      if (status) atomicOr(status, B200EMB_STATUS_BARRIER_TIMEOUT);
+      break;
+    }
+    __nanosleep(64);
+  }
+}
+
 // one thread per rank / owner; world <= 1024
 __global__ void k_exchange_maps(const int64_t* __restrict__ tab, int world, int cols, int rank,
                                 const int64_t* __restrict__ pi, const int64_t* __restrict__ pu,
@@ -66,6 +91,23 @@ int b200emb_exchange_maps(const int64_t* split_table, int world, int cols, int r
   k_exchange_maps<<<1, ((world + 1 + 31) / 32) * 32, 0, static_cast<cudaStream_t>(stream)>>>(
       split_table, world, cols, rank, peer_i_ptrs, peer_u_ptrs, peer_g_ptrs, row_bytes, out);
   return cudaGetLastError() == cudaSuccess ? B200EMB_OK : B200EMB_E_CUDA;
+}
+
+int b200emb_peer_allgather_i64(const int64_t* row, int cols, void* const* table_ptrs,
+                               const int64_t* local_table, void* const* flag_ptrs, int world, int rank,
+                               uint64_t epoch, int64_t* host_copy, int32_t* status, void* stream) {
+  if (!row || !table_ptrs || !flag_ptrs || cols < 1 || cols > 4096 || world < 1 || world > 1024 || rank < 0 ||
+      rank >= world || (host_copy && !local_table))
+    return B200EMB_E_INVALID;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  k_peer_allgather<<<1, ((world + 31) / 32) * 32, 0, s>>>(
+      row, cols, reinterpret_cast<int64_t* const*>(table_ptrs),
+      reinterpret_cast<unsigned long long* const*>(flag_ptrs), world, rank, epoch, status);
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess && host_copy)
+    e = cudaMemcpyAsync(host_copy, local_table, sizeof(int64_t) * static_cast<size_t>(world) * cols,
+                        cudaMemcpyDeviceToHost, s);
+  return e == cudaSuccess ? B200EMB_OK : B200EMB_E_CUDA;
 }
 
 int b200emb_peer_barrier(void* const* flag_ptrs, int world, int rank, uint64_t epoch,

@@ -182,6 +182,28 @@ class ShardedTable:
                 self.peer_i_ptr.append(capi.peer_open(hi))
                 peer_f_ptr.append(capi.peer_open(hf))
         self.peer_f_ptr_t = torch.tensor(peer_f_ptr, dtype=torch.int64, device=self.device)
+        # split-size all-gather over peer memory: two tables (even / odd step) of world rows x 2(world+1)
+        # int64, and a flag array of its own
+        self.ag_cols = 2 * (self.world + 1)
+        tbytes = self.world * self.ag_cols * 8
+        self.peer_t = [capi.PeerBuffer(max(tbytes, 256)) for _ in range(2)]
+        self.peer_af = capi.PeerBuffer(max(self.world * 8, 256))
+        self.peer_af.tensor((max(self.world, 32),), torch.int64).zero_()
+        torch.cuda.synchronize(self.device)
+        h2 = [None] * self.world
+        dist.all_gather_object(h2, (self.peer_t[0].handle, self.peer_t[1].handle, self.peer_af.handle),
+                               group=self.group)
+        t_ptr, af_ptr = [[], []], []
+        for r, (h0, h1, ha) in enumerate(h2):
+            mine = r == self.rank
+            t_ptr[0].append(self.peer_t[0].ptr if mine else capi.peer_open(h0))
+            t_ptr[1].append(self.peer_t[1].ptr if mine else capi.peer_open(h1))
+            af_ptr.append(self.peer_af.ptr if mine else capi.peer_open(ha))
+        self.peer_t_ptr_t = [torch.tensor(p, dtype=torch.int64, device=self.device) for p in t_ptr]
+        self.peer_af_ptr_t = torch.tensor(af_ptr, dtype=torch.int64, device=self.device)
+        self.ag_epoch = 0
+        self._slots = [None] * 4          # preallocated outputs of prepare(), used round-robin
+        self._slot = -1
         self.barrier_epoch = 0
         self.barrier_status = torch.zeros(1, dtype=torch.int32, device=self.device)
         # collective fallback (A/B switch): a 4-byte all_reduce
@@ -204,11 +226,13 @@ class ShardedTable:
                                    self.barrier_status)
 
     # ------------------------------------------------------------------ forward
-    def prepare(self, ids, ws, deterministic=False, stream=None):
+    def prepare(self, ids, ws, deterministic=False, stream=None, after=None):
         """The ids-only part of lookup(): sort plan + de-duplication in `ws`, the split sizes of every rank
         (one all_gather) and their copy to the host.  Needs nothing but the ids, so a training loop can run
         it for batch i+1 on a side `stream` while batch i is still in flight (a data-loader prefetch); the
         host then finds the sizes already there instead of stalling the device queue on a mid-step read."""
+        if self.peer and ids.is_cuda and not self.nccl_barrier:
+            return self._prepare_peer(ids, ws, deterministic, stream, after)
         cur = torch.cuda.current_stream(ids.device) if ids.is_cuda else None
         use = stream if (stream is not None and ids.is_cuda) else None
         if use is not None:
@@ -251,6 +275,44 @@ class ShardedTable:
                     t.record_stream(cur)
         return {"ids": ids, "ws": ws, "deterministic": deterministic, "bounds": bounds, "ebounds": ebounds,
                 "local": local, "table_d": table_d, "table": table, "event": event, "stream": use, "maps": maps}
+
+    def _prepare_peer(self, ids, ws, deterministic, stream, after):
+        """prepare() when the peer buffers exist: three library calls on `stream` (plan + de-duplication,
+        all-gather of the split sizes over peer memory incl. the copy to pinned host memory, scatter maps),
+        all outputs preallocated — the host spends a few tens of microseconds here."""
+        capi, w, n = self.ops.capi, self.world, ids.numel()
+        self._slot = (self._slot + 1) % len(self._slots)
+        sl = self._slots[self._slot]
+        if sl is None or sl["ukeys"].numel() < max(n, 1):
+            dev = ids.device
+            sl = self._slots[self._slot] = {
+                "ukeys": torch.empty(max(n, 1), dtype=torch.int64, device=dev),
+                "local": torch.empty(max(n, 1), dtype=torch.int64, device=dev),
+                "n_unique": torch.zeros(1, dtype=torch.int64, device=dev),
+                "row": torch.zeros(self.ag_cols, dtype=torch.int64, device=dev),     # bounds | elem bounds
+                "maps": torch.empty((4, w + 1), dtype=torch.int64, device=dev),
+                "host": torch.empty((w, self.ag_cols), dtype=torch.int64).pin_memory(),
+                "event": torch.cuda.Event(),
+            }
+        if stream is not None:
+            stream.wait_stream(after if after is not None else torch.cuda.current_stream(ids.device))
+        bounds, ebounds = sl["row"][: w + 1], sl["row"][w + 1:]
+        capi.plan_unique_rows(ids, self.height, w, ws, want_elem_bounds=deterministic,
+                              out=(sl["ukeys"], sl["n_unique"], bounds, ebounds, sl["local"]), stream=stream)
+        self.ag_epoch += 1
+        par = self.ag_epoch & 1
+        local_table = self.peer_t[par].tensor((w, self.ag_cols), torch.int64)
+        capi.peer_allgather_i64(sl["row"], self.peer_t_ptr_t[par], local_table, self.peer_af_ptr_t, w, self.rank,
+                                self.ag_epoch, host_copy=sl["host"], status=self.barrier_status, stream=stream)
+        m = capi.exchange_maps(local_table, self.rank, self.peer_i_ptr_t, self.peer_u_ptr_t, self.peer_g_ptr_t,
+                               self.row_bytes, out=sl["maps"], stream=stream)
+        sl["event"].record(stream if stream is not None else torch.cuda.current_stream(ids.device))
+        maps = {"all": m, "id_dst": m[0, :w], "seg_start": m[1], "seg_dst": m[2, :w], "shard_dst": m[3, :w]}
+        g1 = w + 1
+        return {"ids": ids, "ws": ws, "deterministic": deterministic, "bounds": bounds,
+                "ebounds": ebounds if deterministic else None, "local": sl["local"], "table_d": local_table,
+                "table": sl["host"], "event": sl["event"], "stream": stream, "maps": maps,
+                "cols": g1 * (2 if deterministic else 1)}
 
     def lookup(self, ids, ws, deterministic=False, prep=None, owner_ws=None, owner_stream=None):
         """ids: int64 [n] on this rank.  Returns (out [n, d], ctx for update()).  `prep` = the result of
@@ -296,11 +358,19 @@ class ShardedTable:
             cur = torch.cuda.current_stream(ids.device)
             if owner_stream is not None:
                 owner_stream.wait_stream(cur)
-            with (torch.cuda.stream(owner_stream) if owner_stream is not None else contextlib.nullcontext()):
-                with self._phase("owner sort plan (ids only)"):
-                    self.ops.capi.plan_rows(recv_local, self.hs, owner_ws)
-                owner_plan = torch.cuda.Event()
-                owner_plan.record()
+            if self.phase_events is not None:
+                with (torch.cuda.stream(owner_stream) if owner_stream is not None else contextlib.nullcontext()):
+                    with self._phase("owner sort plan (ids only)"):
+                        self.ops.capi.plan_rows(recv_local, self.hs, owner_ws)
+            else:
+                self.ops.capi.plan_rows(recv_local, self.hs, owner_ws, stream=owner_stream)
+            owner_plan = self._owner_events[self._owner_slot] if hasattr(self, "_owner_events") else None
+            if owner_plan is None:
+                self._owner_events = [torch.cuda.Event() for _ in range(4)]
+                self._owner_slot = 0
+                owner_plan = self._owner_events[0]
+            self._owner_slot = (self._owner_slot + 1) % 4
+            owner_plan.record(owner_stream if owner_stream is not None else cur)
             if owner_stream is not None:
                 recv_local.record_stream(owner_stream)
         if fused:

@@ -56,12 +56,13 @@ def run(args):
     # free — so the host finds the sizes of the next batch already copied and never stalls the device queue.
     side = torch.cuda.Stream(dev)
     side2 = torch.cuda.Stream(dev)
+    main_s = torch.cuda.current_stream(dev)
     prefetch = os.environ.get("B200EMB_NO_PREFETCH") is None
 
     def step(b, prep=None, next_b=None, ids_b=None, dout_b=None):
         i = ids[b] if ids_b is None else ids_b
         g_ = dout[b] if dout_b is None else dout_b
-        nxt = tab.prepare(ids[next_b], ws[next_b], stream=side) if (prefetch and next_b is not None) else None
+        nxt = tab.prepare(ids[next_b], ws[next_b], stream=side, after=main_s) if (prefetch and next_b is not None) else None
         out, ctx = tab.lookup(i, ws[b], prep=prep, owner_ws=state["owner_ws"] if prefetch else None,
                               owner_stream=side2)
         need = sum(ctx["recv"])
@@ -74,7 +75,7 @@ def run(args):
     def run_steps(k):
         """k consecutive steps; exactly k plans are issued inside the call (the first one inline-ahead,
         none after the last step)."""
-        prep = tab.prepare(ids[0], ws[0], stream=side) if prefetch else None
+        prep = tab.prepare(ids[0], ws[0], stream=side, after=main_s) if prefetch else None
         out = ctx = None
         for i in range(k):
             nb = (i + 1) % N_ROTATE if i + 1 < k else None
@@ -95,7 +96,7 @@ def run(args):
         pr.enable()
         run_steps(args.steps)
         pr.disable()
-        pstats.Stats(pr, stream=sys.stderr).sort_stats("tottime").print_stats(28)
+        pstats.Stats(pr, stream=sys.stderr).sort_stats(os.environ.get("B200EMB_PROFILE_SORT", "tottime")).print_stats(45)
     else:
         run_steps(args.steps)
     e1.record()
