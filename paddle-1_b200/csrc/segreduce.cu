@@ -187,6 +187,13 @@ __device__ __forceinline__ void consume(const Params<T>& P, uint32_t key, uint32
   apply_state<T, OP, LPR, NV, VEC>(P, key, eref, col0, l, acc, st);
 }
 
+// Resident CTAs per SM the register allocation aims for.  The MergeAdd consumer keeps no state rows in
+// registers and fits 80 registers without spilling, so it runs 3 CTAs per SM (measured: the sharded
+// path's local MergeAdd 6 % faster); the optimizer consumers spill at that size and lose (C3 +9 %), so they
+// keep 128 registers and 2 CTAs.
+template <UpdateOp OP, int NV>
+constexpr int chunk_min_ctas() { return (OP == UpdateOp::kMergeAdd && NV <= 2) ? 3 : 2; }
+
 // Closes one chain: the segment that leaves CTA `c` (tail carry) and enters the next `len` CTAs
 // (head carries).  Run by the LAST CTA of the chain to arrive, with the whole CTA: the lane
 // groups sum the head rows strided by group with all loads in flight, group 0 adds the per-group
@@ -263,7 +270,7 @@ __device__ __forceinline__ void close_chain(int c, int len, uint32_t key, uint32
 
 // ------------------------------------------------------------------------------------------
 template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
-__global__ void __launch_bounds__(kBlock, 2)
+__global__ void __launch_bounds__(kBlock, chunk_min_ctas<OP, NV>())
 k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ perm, int n,
                int chunk, const T* __restrict__ value, Params<T> P, Carry<T> C) {
   constexpr int EPV = Epv<T, VEC>::value;
@@ -620,17 +627,10 @@ cudaError_t launch_op(const SortedPlan& plan, const T* value, int64_t n, int64_t
           plan.keys, plan.perm, ni, reinterpret_cast<const uint32_t*>(ws + L.off_seg_start),
           reinterpret_cast<const PlanHeader*>(ws + L.off_plan), value, P);
     } else {
-      // one wave: as many lane groups as the chip holds at this kernel's real occupancy
-      static thread_local int occ_cache = 0;
-      if (occ_cache == 0) {
-        int occ = 0;
-        const size_t probe = sizeof(T) * 2 * GPC * COLS + sizeof(uint32_t) * 2 * GPC * 16;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(
-                &occ, k_chunk_reduce<T, OP, LPR, NV, VEC>, kBlock, probe) != cudaSuccess || occ < 1)
-          occ = 4;
-        occ_cache = occ;
-      }
-      int chunk = choose_chunk(n, GPC * occ_cache);
+      // one wave of lane groups at 2 CTAs per SM.  The chunk size fixes the summation tree, so it must
+      // depend on (N, D) alone — not on the consumer or its register count (MergeAdd fits 3 CTAs per SM;
+      // the fast-mode optimizers must still reduce in exactly MergeAdd's order).
+      int chunk = choose_chunk(n, GPC * 2);
       if (const char* ov = std::getenv("B200EMB_CHUNK")) {  // tuning override
         const int c = std::atoi(ov);
         if (c >= kMinChunk && c <= kMaxChunk) chunk = c;
