@@ -198,3 +198,44 @@ def test_split_ids_merge_ids_reference_semantics(capi, goldens):
         x = np.concatenate(blocks)
         merged = capi.merge_ids(torch.from_numpy(x).cuda(), shards, ws).cpu().numpy()
         assert np.array_equal(merged, oracle.merge_ids(ids, blocks))
+
+
+def test_exchange_maps_matches_numpy(capi):
+    """b200emb_exchange_maps is a pure function of the gathered split table: check it against numpy for
+    every rank of a made-up 5-rank table (the pointers are just integers here)."""
+    rng = np.random.default_rng(9)
+    world, row_bytes = 5, 256
+    cols = 2 * (world + 1)
+    tab = np.zeros((world, cols), np.int64)
+    tab[:, 1:world + 1] = np.cumsum(rng.integers(0, 1000, (world, world)), axis=1)
+    pi, pu, pg = (rng.integers(1 << 20, 1 << 40, world) * 256 for _ in range(3))
+    tab_d = torch.from_numpy(tab).cuda()
+    ptrs = [torch.from_numpy(np.asarray(p, np.int64)).cuda() for p in (pi, pu, pg)]
+    for rank in range(world):
+        got = capi.exchange_maps(tab_d, rank, ptrs[0], ptrs[1], ptrs[2], row_bytes).cpu().numpy()
+        before = (tab[:rank, 1:world + 1] - tab[:rank, :world]).sum(axis=0)
+        cnt = tab[:, rank + 1] - tab[:, rank]
+        assert np.array_equal(got[0, :world], pi + 8 * before)
+        assert np.array_equal(got[1], np.concatenate([[0], np.cumsum(cnt)]))
+        assert np.array_equal(got[2, :world], pu + row_bytes * tab[:, rank])
+        assert np.array_equal(got[3, :world], pg + row_bytes * before)
+
+
+def test_peer_barrier_and_allgather_single_rank(capi):
+    """world = 1: the peer kernels talk to this GPU's own buffers (the multi-GPU tests cover the real thing)."""
+    flags = torch.zeros(32, dtype=torch.int64, device="cuda")
+    table = torch.zeros((1, 6), dtype=torch.int64, device="cuda")
+    fp = torch.tensor([flags.data_ptr()], dtype=torch.int64, device="cuda")
+    tp = torch.tensor([table.data_ptr()], dtype=torch.int64, device="cuda")
+    status = capi.new_status()
+    for epoch in (1, 2, 3):
+        capi.peer_barrier(fp, 1, 0, epoch, status)
+    assert int(flags[0].item()) == 3
+    row = torch.arange(10, 16, dtype=torch.int64, device="cuda")
+    host = torch.zeros((1, 6), dtype=torch.int64).pin_memory()
+    capi.peer_allgather_i64(row, tp, table, fp, 1, 0, 4, host_copy=host, status=status)
+    torch.cuda.synchronize()
+    assert host.reshape(-1).tolist() == list(range(10, 16)) and torch.equal(table.reshape(-1), row)
+    assert int(status.item()) == 0
+    with pytest.raises(capi.B200EmbError):
+        capi.peer_barrier(fp, 1, 1, 5, status)       # rank outside the world
