@@ -5,7 +5,7 @@
 // original order (operators/merge_ids_op.h:63-87).  Instead of a separate bucketing pass, ids are
 // sorted once by key = owner * shard_height + local_row (KeyMap, internal.h): that one plan
 //   - groups the ids by destination GPU (contiguous key ranges) and de-duplicates them
-//     (k_head_scan) so each unique row crosses NVLink once per direction,
+//     (k_head_count / k_head_write) so each unique row crosses NVLink once per direction,
 //   - is the plan of the local MergeAdd that pre-reduces the gradient before it is sent,
 //   - and its (uidx, perm) pair is the inverse map that expands the returned unique rows back to
 //     the batch order (k_expand_unique = merge_ids).
