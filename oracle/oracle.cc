@@ -11,7 +11,7 @@
 // multiply-add is ever contracted.
 //
 // Parity is PINNED: (1) by the hand-written constants of the reference's own
-// tests, restated as tests/golden/*.json (G1..G10 of SURVEY.md §8c), and
+// tests, restated as tests/golden/*.json (G1..G10 of SURVEY.md §8c, G11), and
 // (2) in the build container by oracle/_ref, the reference's unmodified CPU
 // kernels compiled from /root/reference (see oracle/Makefile, tests/test_ref_*).
 //

@@ -1,4 +1,4 @@
-"""Pins the CPU oracle against the reference's own known-answer tests.
+"""Pins the CPU oracle against the reference's own known-answer tests (plus G11).
 CPU only.  Each test names the reference test it restates."""
 import math
 
