@@ -473,7 +473,7 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
   if (num_ctas == 1) return;
 
   // ---- arrivals -----------------------------------------------------------------------------------
-  __threadfence();                       // this CTA's carry rows are visible before it counts itself in
+  if (!has_head && !has_tail) return;    // no segment crosses this CTA's boundaries
   if (warp == 0 && has_head) {           // CTAs of the chain before this one
     const uint32_t stop = __ballot_sync(0xffffffffu, !probe);
     int before = stop ? __ffs(stop) : 0;
@@ -490,6 +490,9 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
   }
   __syncthreads();
   if (tid == 0) {
+    // Every thread's carry stores happen before the barrier above; this one fence (cumulative) publishes
+    // them device-wide before the CTA counts itself in — the grid-sync idiom, one MEMBAR per CTA instead of 256.
+    __threadfence();
     int nfix = 0;
     if (has_head) {
       const int c0 = cta - s_before, members = s_before + (through ? s_after : 0) + 1;
