@@ -127,8 +127,9 @@ def alloc_workspace(n, d, elem_size=4, device="cuda"):
 
 
 def alloc_workspace_upto(n_max, d, elem_size=4, device="cuda"):
-    """Workspace valid for ANY n <= n_max (the requirement grows monotonically with n)."""
-    nbytes = max(workspace_bytes(n_max, d, elem_size), 256)
+    """Workspace valid for ANY n <= n_max.  The sort uses 1024-key tiles up to 1 212 416 ids and 2048-key
+    tiles above (sort.cu sort_tile_keys), so the requirement is not monotonic across that boundary."""
+    nbytes = max(workspace_bytes(n_max, d, elem_size), workspace_bytes(min(n_max, 148 * 4 * 2 * 1024), d, elem_size), 256)
     return torch.empty(nbytes, dtype=torch.uint8, device=device)
 
 

@@ -54,7 +54,7 @@ __device__ __forceinline__ void ld_cg_vec(const uint32_t* p, uint32_t (&v)[K]) {
 // Launches per plan: 1 + passes, no memset, no look-back.
 constexpr int kDirectMaxTiles = 64;
 
-template <int BITS>
+template <int BITS, int ITEMS>
 __global__ void __launch_bounds__(kSortThreads, 4)
 k_prepare_direct(const int64_t* __restrict__ rows, int n, uint32_t height, KeyMap km, int passes,
                  uint32_t* __restrict__ keys, uint32_t* __restrict__ hmat, size_t per_pass,
@@ -69,8 +69,8 @@ k_prepare_direct(const int64_t* __restrict__ rows, int n, uint32_t height, KeyMa
   __syncthreads();
   bool bad = false;
 #pragma unroll
-  for (int j = 0; j < kSortItems; ++j) {
-    const int i = tile * kSortTile + j * kSortThreads + tid;
+  for (int j = 0; j < ITEMS; ++j) {
+    const int i = tile * (ITEMS * kSortThreads) + j * kSortThreads + tid;
     const bool valid = i < n;
     uint32_t key = 0;
     if (valid) {
@@ -158,7 +158,7 @@ k_colscan(uint32_t* __restrict__ hmat, int tiles, int bins) {
   if (warp == 0 && r == 0) col[static_cast<size_t>(tiles) * bins] = total;
 }
 
-template <int BITS, bool HAS_PERM_IN, bool SCANNED>
+template <int BITS, bool HAS_PERM_IN, bool SCANNED, int ITEMS>
 __global__ void __launch_bounds__(kSortThreads, 4)   // <= 64 registers: fits beside the row kernels on an SM
 k_radix_pass_direct(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ perm_in,
                     uint32_t* __restrict__ keys_out, uint32_t* __restrict__ perm_out, int n,
@@ -175,11 +175,11 @@ k_radix_pass_direct(const uint32_t* __restrict__ keys_in, const uint32_t* __rest
     uint32_t* z = reinterpret_cast<uint32_t*>(s_cnt);
     for (int i = tid; i < kWarps * kBins / 2; i += kSortThreads) z[i] = 0;
   }
-  const int warp_start = tile * kSortTile + warp * (32 * kSortItems);
+  const int warp_start = tile * (ITEMS * kSortThreads) + warp * (32 * ITEMS);
   uint16_t* my_cnt = s_cnt + warp * kBins;
-  uint32_t key[kSortItems], pm[kSortItems], rank[kSortItems];
+  uint32_t key[ITEMS], pm[ITEMS], rank[ITEMS];
 #pragma unroll
-  for (int j = 0; j < kSortItems; ++j) {
+  for (int j = 0; j < ITEMS; ++j) {
     const int idx = warp_start + j * 32 + lane;
     const bool valid = idx < n;
     key[j] = valid ? keys_in[idx] : 0u;
@@ -219,7 +219,7 @@ k_radix_pass_direct(const uint32_t* __restrict__ keys_in, const uint32_t* __rest
   // stable rank inside the warp: items are ordered (j, lane) == ascending idx
   const uint32_t lt = lanemask_lt();
 #pragma unroll
-  for (int j = 0; j < kSortItems; ++j) {
+  for (int j = 0; j < ITEMS; ++j) {
     const bool valid = (warp_start + j * 32 + lane) < n;
     const uint32_t digit = (key[j] >> shift) & (kBins - 1);
     const uint32_t peers = match_digit<BITS>(digit, valid);
@@ -268,7 +268,7 @@ k_radix_pass_direct(const uint32_t* __restrict__ keys_in, const uint32_t* __rest
   }
   __syncthreads();
 #pragma unroll
-  for (int j = 0; j < kSortItems; ++j) {
+  for (int j = 0; j < ITEMS; ++j) {
     const int idx = warp_start + j * 32 + lane;
     if (idx < n) {
       const uint32_t digit = (key[j] >> shift) & (kBins - 1);
@@ -277,7 +277,7 @@ k_radix_pass_direct(const uint32_t* __restrict__ keys_in, const uint32_t* __rest
       perm_out[pos] = pm[j];
       if (hnext) {
         const uint32_t nd = (key[j] >> (shift + BITS)) & (kBins - 1);
-        atomicAdd(hnext + static_cast<size_t>(pos / kSortTile) * kBins + nd, 1u);
+        atomicAdd(hnext + static_cast<size_t>(pos / (ITEMS * kSortThreads)) * kBins + nd, 1u);
       }
     }
   }
@@ -397,6 +397,14 @@ int key_bits(int64_t height) {  // keys span [0, height] (height = the invalid s
 // Digits of up to 10 bits (20 KB of shared counters per CTA) to save passes; the fewest passes
 // that cover the key, then the narrowest digit that still fits them.
 constexpr int kMaxDigitBits = 10;
+// Keys per tile.  Batches between the direct mode and about two resident waves of 2048-key tiles are
+// latency-bound with half-empty SMs (320 tiles at C3: 15 % issue utilisation): 1024-key tiles double
+// the CTAs in flight there.  Larger batches fill the chip anyway and keep the smaller count matrix.
+constexpr int64_t kHalfTileMaxKeys = 148LL * 4 * 2 * 1024;
+int64_t sort_tile_keys(int64_t n) {
+  if (ceil_div(n, kSortTile) <= kDirectMaxTiles || n > kHalfTileMaxKeys) return kSortTile;
+  return kSortTile / 2;
+}
 struct DigitPlan { int passes, bits; bool direct; };
 DigitPlan digit_plan(int64_t n, int64_t height) {
   const int kb = key_bits(height);
@@ -416,7 +424,7 @@ static_assert(kMaxPasses * (1 << kRadixBits) <= kDigitWordsPerTile, "4 passes of
 Workspace make_workspace(int64_t n, int64_t d, int64_t elem_size) {
   Workspace L{};
   if (n < 1) n = 1;
-  L.sort_tiles = ceil_div(n, kSortTile);
+  L.sort_tiles = ceil_div(n, sort_tile_keys(n));
   L.scan_tiles = ceil_div(n, kScanTile);
   L.max_ctas = ceil_div(n, static_cast<int64_t>(kMinGroupsPerCta) * kMinChunk) + 1;
   size_t off = 0;
@@ -444,7 +452,7 @@ SortedPlan plan_view(int64_t n, int64_t height, char* ws, const Workspace& L) {
 }
 
 namespace {
-template <int BITS, bool SCANNED>
+template <int BITS, bool SCANNED, int ITEMS>
 cudaError_t launch_passes_direct(const int64_t* rows, int n, uint32_t height, KeyMap km, int passes,
                                  char* ws, const Workspace& L, int32_t* status, cudaStream_t s) {
   constexpr int kBins = 1 << BITS;
@@ -455,7 +463,7 @@ cudaError_t launch_passes_direct(const int64_t* rows, int n, uint32_t height, Ke
   uint32_t* hmat = reinterpret_cast<uint32_t*>(ws + L.off_digit_counts);
   const int tiles = static_cast<int>(L.sort_tiles);
   const size_t per_pass = static_cast<size_t>(tiles + 1) * kBins;   // + the totals row
-  k_prepare_direct<BITS><<<tiles, kSortThreads, 0, s>>>(
+  k_prepare_direct<BITS, ITEMS><<<tiles, kSortThreads, 0, s>>>(
       rows, n, height, km, passes, keys[0], hmat, per_pass,
       reinterpret_cast<uint32_t*>(ws + L.off_cta_arrive), static_cast<int>(L.max_ctas), status);
   for (int p = 0; p < passes; ++p) {
@@ -463,10 +471,10 @@ cudaError_t launch_passes_direct(const int64_t* rows, int n, uint32_t height, Ke
     if constexpr (SCANNED)
       k_colscan<<<kBins / kColscanBins, kColscanThreads, 0, s>>>(hmat + p * per_pass, tiles, kBins);
     if (p == 0)
-      k_radix_pass_direct<BITS, false, SCANNED><<<tiles, kSortThreads, 0, s>>>(
+      k_radix_pass_direct<BITS, false, SCANNED, ITEMS><<<tiles, kSortThreads, 0, s>>>(
           keys[0], nullptr, keys[1], perm[1], n, 0, hmat, hn);
     else
-      k_radix_pass_direct<BITS, true, SCANNED><<<tiles, kSortThreads, 0, s>>>(
+      k_radix_pass_direct<BITS, true, SCANNED, ITEMS><<<tiles, kSortThreads, 0, s>>>(
           keys[p & 1], perm[p & 1], keys[(p + 1) & 1], perm[(p + 1) & 1], n, p * BITS,
           hmat + p * per_pass, hn);
   }
@@ -502,17 +510,24 @@ cudaError_t launch_plan(const int64_t* rows, int64_t n, int64_t height, char* ws
   const int ni = static_cast<int>(n);
   const uint32_t h = static_cast<uint32_t>(height);
   cudaError_t e;
+  const bool half = sort_tile_keys(n) != kSortTile;
   if (dp.direct) {
     switch (dp.bits) {
-      case 8: e = launch_passes_direct<8, false>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
-      case 9: e = launch_passes_direct<9, false>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
-      default: e = launch_passes_direct<10, false>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
+      case 8: e = launch_passes_direct<8, false, kSortItems>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
+      case 9: e = launch_passes_direct<9, false, kSortItems>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
+      default: e = launch_passes_direct<10, false, kSortItems>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
+    }
+  } else if (half) {
+    switch (dp.bits) {
+      case 8: e = launch_passes_direct<8, true, kSortItems / 2>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
+      case 9: e = launch_passes_direct<9, true, kSortItems / 2>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
+      default: e = launch_passes_direct<10, true, kSortItems / 2>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
     }
   } else {
     switch (dp.bits) {
-      case 8: e = launch_passes_direct<8, true>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
-      case 9: e = launch_passes_direct<9, true>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
-      default: e = launch_passes_direct<10, true>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
+      case 8: e = launch_passes_direct<8, true, kSortItems>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
+      case 9: e = launch_passes_direct<9, true, kSortItems>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
+      default: e = launch_passes_direct<10, true, kSortItems>(rows, ni, h, km, dp.passes, ws, L, status, s); break;
     }
   }
   if (e != cudaSuccess) return e;
