@@ -20,7 +20,6 @@ constexpr int64_t kIdSpace = 0xFFFFFFFELL;   // ids are sorted as 32-bit keys in
 
 template <typename T> struct GatherApi;      // "lookup_table" over raw 4- and 8-byte elements
 template <> struct GatherApi<float> { static constexpr auto fn = b200emb_lookup_table_f32; using U = float; };
-template <> struct GatherApi<double> { static constexpr auto fn = b200emb_lookup_table_f64; using U = double; };
 template <> struct GatherApi<int64_t> { static constexpr auto fn = b200emb_lookup_table_f64; using U = double; };
 template <typename T> struct MergeApi;
 template <> struct MergeApi<float> { static constexpr auto fn = b200emb_merge_ids_f32; };
