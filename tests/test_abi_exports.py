@@ -35,6 +35,24 @@ def test_workspace_bytes_is_monotonic_and_aligned(pkg):
     assert w(-1, 64) == 0 and w(10, 0) == 0 and w(10, 4, 3) == 0
 
 
+def test_workspace_for_a_range_of_batch_sizes(pkg, monkeypatch):
+    """alloc_workspace_upto(n_max) must cover every n <= n_max although the sort switches from 1024- to
+    2048-key tiles above 1 212 416 ids, which makes the requirement drop there (host-only arithmetic)."""
+    pkg.build_native()
+    capi = pkg.capi
+    edge = 148 * 4 * 2 * 1024
+    assert capi.workspace_bytes(edge, 64) > capi.workspace_bytes(edge + 1, 64)      # the non-monotonic spot
+    sizes = {}
+    import torch
+    monkeypatch.setattr(torch, "empty", lambda nbytes, **kw: sizes.setdefault("n", nbytes))
+    for n_max in (1000, 131072, 131073, edge - 5, edge, edge + 1, 1703936, 3 * edge):
+        sizes.clear()
+        capi.alloc_workspace_upto(n_max, 64, 4, "cpu")
+        probe = {1, n_max // 3, n_max // 2, n_max - 1, n_max, min(n_max, 131072), min(n_max, 131073), min(n_max, edge),
+                 min(n_max, edge + 1)}
+        assert all(capi.workspace_bytes(max(n, 1), 64) <= sizes["n"] for n in probe), n_max
+
+
 def test_argument_errors_without_a_gpu(pkg):
     pkg.build_native()
     lib = pkg.capi.lib()
