@@ -192,6 +192,10 @@ int b200emb_plan_unique_rows(const int64_t* rows, int64_t n, int64_t height, int
   if (e != cudaSuccess) return fail_cuda(e);
   e = launch_head_scan(plan, n, static_cast<uint32_t>(plan_height), ws, L, unique_keys, n_unique, s);
   if (e != cudaSuccess) return fail_cuda(e);
+  // batch position -> unique index, kept in the position buffer the sort no longer needs (expand_unique)
+  e = launch_inverse_map(plan, reinterpret_cast<const uint32_t*>(ws + L.off_uidx), n,
+                         reinterpret_cast<uint32_t*>(ws + L.off_perm[(plan.passes & 1) ^ 1]), s);
+  if (e != cudaSuccess) return fail_cuda(e);
   if (shard_bounds || elem_bounds || local_rows) {
     if (!unique_keys) return B200EMB_E_INVALID;   // the split reads the unique keys
     e = launch_shard_split(unique_keys, plan, ws, L, static_cast<int>(num_shards),
@@ -215,7 +219,11 @@ int run_permute(const T* src, int64_t n, int64_t d, int64_t plan_height, void* w
   rc = check_workspace(workspace, workspace_bytes, L);
   if (rc != B200EMB_OK) return rc;
   char* ws = static_cast<char*>(workspace);
-  const SortedPlan plan = plan_view(n, plan_height, ws, L);
+  SortedPlan plan = plan_view(n, plan_height, ws, L);
+  if (mode == 1) {   // expand_unique: out[i,:] = src[inv[i],:], a gather by the inverse map of plan_unique_rows
+    plan.perm = reinterpret_cast<const uint32_t*>(ws + L.off_perm[(plan.passes & 1) ^ 1]);
+    mode = 0;
+  }
   cudaError_t e = launch_permute_rows<T>(src, plan, reinterpret_cast<const uint32_t*>(ws + L.off_uidx), n,
                                          d, out, mode, static_cast<cudaStream_t>(stream));
   return e == cudaSuccess ? B200EMB_OK : fail_cuda(e);

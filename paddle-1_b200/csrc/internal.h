@@ -132,6 +132,8 @@ cudaError_t launch_update(const SortedPlan& plan, const T* value, int64_t n, int
 int choose_chunk(int64_t n, int groups_per_sm);
 
 // shard.cu
+cudaError_t launch_inverse_map(const SortedPlan& plan, const uint32_t* uidx, int64_t n, uint32_t* inv,
+                               cudaStream_t s);
 cudaError_t launch_shard_split(const int64_t* ukeys, const SortedPlan& plan, char* ws,
                                const Workspace& L, int shards, uint32_t shard_height, int64_t n,
                                uint32_t invalid_key, int64_t* bounds, int64_t* elem_bounds,

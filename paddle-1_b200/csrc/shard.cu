@@ -118,7 +118,23 @@ k_permute_rows(const T* __restrict__ src, const uint32_t* __restrict__ perm,
   }
 }
 
+// inv[position in the batch] = unique index of that id: the plan's (perm, uidx) pair turned around, so that
+// the expansion to batch order can walk the OUTPUT sequentially (streaming stores) instead of scattering rows
+__global__ void __launch_bounds__(256)
+k_inverse_map(const uint32_t* __restrict__ perm, const uint32_t* __restrict__ uidx, int n,
+              uint32_t* __restrict__ inv) {
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) inv[perm[e]] = uidx[e];
+}
+
 }  // namespace
+
+cudaError_t launch_inverse_map(const SortedPlan& plan, const uint32_t* uidx, int64_t n, uint32_t* inv,
+                               cudaStream_t s) {
+  if (n == 0) return cudaSuccess;
+  const int grid = static_cast<int>(std::min<int64_t>(ceil_div(n, 256), 148 * 8));
+  k_inverse_map<<<grid, 256, 0, s>>>(plan.perm, uidx, static_cast<int>(n), inv);
+  return cudaGetLastError();
+}
 
 cudaError_t launch_shard_split(const int64_t* ukeys, const SortedPlan& plan, char* ws,
                                const Workspace& L, int shards, uint32_t shard_height, int64_t n,
