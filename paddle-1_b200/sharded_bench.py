@@ -153,9 +153,11 @@ def run(args):
         b_own = recv_rows * (8 + 2 * 4 * d) + recv_rows * (8 + 4 * d) + recv_rows * 2 * 4 * d
         hbm = (b_req + b_own) / (ms_per_step * 1e-3) / 1e9
         nv = float(sent.item()) / args.steps / (ms_per_step * 1e-3) / 1e9
-        hs = capi.HEAD_SCAN_KERNELS
-        launches = (capi.plan_kernel_count(n, tab.plan_h) + hs) + 1 + 1 + 1 + 1 + 3 + \
-                   (capi.plan_kernel_count(recv_rows, tab.hs) + hs) + 2
+        # this library's kernels per step on the fused path — prepare: sort plan, head scan (2), inverse map,
+        # shard split, split-size all-gather, scatter maps; lookup: id scatter, barrier, owner-side sort plan,
+        # owner gather, barrier, expand; update: MergeAdd + scatter, barrier, owner update
+        launches = (capi.plan_kernel_count(n, tab.plan_h) + capi.HEAD_SCAN_KERNELS + 4) + 2 + \
+                   capi.plan_kernel_count(recv_rows, tab.hs) + 3 + 3
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": warm, "ms_per_step": ms_per_step, "higher_is_better": True,
