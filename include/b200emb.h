@@ -53,7 +53,8 @@ extern "C" {
 
 #define B200EMB_STATUS_BAD_LOOKUP_ID 1
 #define B200EMB_STATUS_BAD_GRAD_ROW 2
-#define B200EMB_STATUS_BARRIER_TIMEOUT 4   /* b200emb_peer_barrier gave up waiting for a rank */
+#define B200EMB_STATUS_BARRIER_TIMEOUT 4   /* a peer barrier / arrival flag gave up waiting for a rank (~20 s) */
+#define B200EMB_STATUS_SHARD_OVERFLOW 8    /* b200emb_shard_*: more rows than the capacities given at create() */
 
 int b200emb_abi_version(void);
 /* cudaError_t of the last failing CUDA call made by this library on the calling thread. */
@@ -252,6 +253,68 @@ int b200emb_peer_allgather_i64(const int64_t* row, int cols, void* const* table_
 int b200emb_exchange_maps(const int64_t* split_table, int world, int cols, int rank,
                           const int64_t* peer_i_ptrs, const int64_t* peer_u_ptrs,
                           const int64_t* peer_g_ptrs, int64_t row_bytes, int64_t* out, void* stream);
+
+/* ---- Row-sharded embedding step ------------------------------------------------------------
+ * The multi-device SelectedRows path of the reference — ReduceOpHandle::RunImpl gathers every device's sparse
+ * gradient on one device (framework/details/reduce_op_handle.cc:88-94, reduce_and_gather.h:56-93), the
+ * optimizer runs there and BroadcastOpHandle::RunImpl copies the parameter back
+ * (framework/details/broadcast_op_handle.cc:71-122), chosen per gradient by multi_devices_graph_pass.cc:411-426
+ * — becomes a table sharded by row over the `world` GPUs of one box: owner(id) = id % world, local row =
+ * id / world (the reference's own convention for its distributed lookup table, operators/split_ids_op.h:45-49),
+ * rows handed back in the requester's order (operators/merge_ids_op.h:63-87).
+ * One engine per rank / GPU; all ranks make the same calls in the same order (SPMD).  The step path never
+ * allocates, never synchronises and reads nothing on the host: kernels of different GPUs meet through
+ * arrival flags in peer memory, each consumer waiting only for the ranks whose data it reads.  float32, fast
+ * (fixed-tree) reduction mode; duplicates are merged locally before they cross NVLink.
+ *
+ * create   (allocates; current device = this rank's GPU).  `shard` = this rank's rows [ceil(height/world), d]
+ *          (row i holds global row i*world + rank), moment1/moment2 alike for Adam (NULL for SGD).
+ *          max_ids_per_step bounds n of prepare(); max_recv_rows bounds the unique rows all ranks together
+ *          request from this owner in one step.  Exceeding either sets B200EMB_STATUS_SHARD_OVERFLOW in the
+ *          status word and drops the excess rows.
+ * export / connect   exchange of the per-rank blocks between processes: export() yields a 64-byte CUDA IPC
+ *          handle; the caller all-gathers the handles with whatever transport it has (NCCL, MPI,
+ *          torch.distributed, Fluid's gen_nccl_id RPC) and passes the world*64 bytes, in rank order, to connect().
+ *          Ranks living in ONE process (ParallelExecutor: one thread per device) pass the block pointers
+ *          (b200emb_shard_block) to connect_ptrs() instead, with peer access enabled by the caller.
+ * prepare  the ids-only part of a step — sort plan, de-duplication, split points per owner — into one of 4
+ *          slots; needs nothing but the ids, so a training loop can run it for batch i+1 on another stream
+ *          while batch i is in flight.  `ids` must stay valid until update() of that slot has run.
+ * lookup   out[k,:] = table[ids[k],:] for the slot's ids (lookup_table_op.h:36-84 over the sharded table).
+ * update   sparse SGD / lazy Adam of the sharded table with the SelectedRows gradient {rows = the slot's ids,
+ *          value = d_out} (sgd_op.h:47-81, adam_op.h:158-220,282-321): merged locally, merged rows sent to
+ *          their owners, fused update there.  lr / beta*_pow are 1-element device tensors.
+ * *_phases run a sub-range of the kernel sequence (lookup: 0 send ids, 1 collect + owner plan, 2 owner gather,
+ *          3 expand; update: 0 merge + send, 1 owner update): a driver that hosts several ranks on ONE GPU
+ *          issues phase k for every rank before phase k+1 (kernels that wait for each other must not share a GPU
+ *          out of order); everybody else calls lookup()/update().
+ * status_ptr  device int32 the kernels OR B200EMB_STATUS_* bits into; read it at your own sync points. */
+typedef struct b200emb_shard b200emb_shard_t;
+#define B200EMB_SHARD_SGD 0
+#define B200EMB_SHARD_ADAM 1
+int b200emb_shard_create(int world, int rank, int64_t height, int64_t d, int optimizer, float* shard,
+                         float* moment1, float* moment2, int64_t max_ids_per_step, int64_t max_recv_rows,
+                         b200emb_shard_t** out);
+int b200emb_shard_export(b200emb_shard_t* sh, unsigned char* handle64);
+int b200emb_shard_connect(b200emb_shard_t* sh, const unsigned char* handles);
+void* b200emb_shard_block(b200emb_shard_t* sh);
+int b200emb_shard_connect_ptrs(b200emb_shard_t* sh, void* const* blocks);
+int b200emb_shard_prepare(b200emb_shard_t* sh, int slot, const int64_t* ids, int64_t n, void* stream);
+int b200emb_shard_lookup(b200emb_shard_t* sh, int slot, float* out, void* stream);
+int b200emb_shard_update(b200emb_shard_t* sh, int slot, const float* d_out, const float* lr,
+                         const float* beta1_pow, const float* beta2_pow, float beta1, float beta2,
+                         float epsilon, void* stream);
+int b200emb_shard_lookup_phases(b200emb_shard_t* sh, int slot, float* out, void* stream, int first, int last);
+int b200emb_shard_update_phases(b200emb_shard_t* sh, int slot, const float* d_out, const float* lr,
+                                const float* beta1_pow, const float* beta2_pow, float beta1, float beta2,
+                                float epsilon, void* stream, int first, int last);
+int32_t* b200emb_shard_status_ptr(b200emb_shard_t* sh);
+/* out8 = {world, rank, shard height, plan height, max ids, per-source id capacity, max recv rows, block bytes} */
+int b200emb_shard_info(b200emb_shard_t* sh, int64_t* out8);
+/* out6 = device pointers {slot's split points int64[world+1], slot's unique count, owner segment starts
+ * int64[world+1], received row ids, step counter u64, status}: for tests and byte accounting after a sync. */
+int b200emb_shard_debug_ptrs(b200emb_shard_t* sh, int slot, void** out6);
+int b200emb_shard_destroy(b200emb_shard_t* sh);
 
 /* scatter::MergeAdd — replaces math/selected_rows_functor.cu:235-297 (CPU semantics
  * selected_rows_functor.cc:193-228): out_rows = ascending unique rows, out_value[u,:] = sum of

@@ -20,7 +20,8 @@ FLUID_LIB_PATH = os.path.join(PKG_DIR, "libb200emb_fluid.so")
 
 NVCC_FLAGS = ["-O3", "-std=c++20", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-fmad=false", "-Xcompiler", "-fPIC", "-shared"]
-KERNEL_SOURCES = ["capi.cu", "sort.cu", "cluster_sort.cu", "gather.cu", "segreduce.cu", "shard.cu", "regularize.cu", "peer.cu", "noalloc.cu"]
+HEADERS = ["common.cuh", "internal.h", "segreduce.cuh"]
+KERNEL_SOURCES = ["capi.cu", "sort.cu", "cluster_sort.cu", "gather.cu", "segreduce_f32.cu", "segreduce_f64.cu", "shard.cu", "regularize.cu", "peer.cu", "noalloc.cu", "shard_engine.cu"]
 
 
 def _nvcc():
@@ -37,14 +38,34 @@ def _stale(target, sources):
     return any(os.path.getmtime(s) > t for s in sources if os.path.exists(s))
 
 
+def _compile_objects(nvcc, flags, srcs, objdir, deps, force, verbose):
+    """One nvcc -c per translation unit, in parallel; an object is rebuilt when its source or a header is newer."""
+    from concurrent.futures import ThreadPoolExecutor
+    os.makedirs(objdir, exist_ok=True)
+    jobs, objs = [], []
+    for s in srcs:
+        o = os.path.join(objdir, os.path.basename(s) + ".o")
+        objs.append(o)
+        if force or _stale(o, [s] + deps):
+            jobs.append([nvcc] + flags + ["-c", s, "-o", o])
+    if verbose:
+        for j in jobs:
+            print(" ".join(j), file=sys.stderr)
+    with ThreadPoolExecutor(max_workers=max(1, min(len(jobs), os.cpu_count() or 1))) as ex:
+        list(ex.map(subprocess.check_call, jobs))
+    return objs, bool(jobs)
+
+
 def build_native(force=False, verbose=False):
     """Compile libb200emb.so (and libb200emb_fluid.so when its sources exist) in-tree for sm_100a."""
     csrc = os.path.join(PKG_DIR, "csrc")
     srcs = [os.path.join(csrc, s) for s in KERNEL_SOURCES]
-    deps = srcs + [os.path.join(csrc, h) for h in ("common.cuh", "internal.h")] + \
-        [os.path.join(ROOT, "include", "b200emb.h")]
-    if force or _stale(LIB_PATH, deps):
-        cmd = [_nvcc()] + NVCC_FLAGS + ["-o", LIB_PATH] + srcs
+    headers = [os.path.join(csrc, h) for h in HEADERS] + [os.path.join(ROOT, "include", "b200emb.h")]
+    compile_flags = [f for f in NVCC_FLAGS if f != "-shared"]
+    objs, rebuilt = _compile_objects(_nvcc(), compile_flags, srcs, os.path.join(PKG_DIR, "build", "csrc"),
+                                     headers, force, verbose)
+    if rebuilt or _stale(LIB_PATH, objs):
+        cmd = [_nvcc(), "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB_PATH] + objs
         if verbose:
             print(" ".join(cmd), file=sys.stderr)
         subprocess.check_call(cmd)

@@ -38,7 +38,13 @@ EXPORTS = [
     "b200emb_sparse_decay_f32", "b200emb_sparse_decay_f64",
     "b200emb_peer_alloc", "b200emb_peer_open", "b200emb_peer_close", "b200emb_peer_free",
     "b200emb_peer_barrier", "b200emb_exchange_maps", "b200emb_peer_allgather_i64",
+    "b200emb_shard_create", "b200emb_shard_export", "b200emb_shard_connect", "b200emb_shard_block",
+    "b200emb_shard_connect_ptrs", "b200emb_shard_prepare", "b200emb_shard_lookup", "b200emb_shard_update",
+    "b200emb_shard_lookup_phases", "b200emb_shard_update_phases", "b200emb_shard_status_ptr",
+    "b200emb_shard_info", "b200emb_shard_debug_ptrs", "b200emb_shard_destroy",
 ]
+STATUS_BARRIER_TIMEOUT = 4
+STATUS_SHARD_OVERFLOW = 8
 
 _lib = None
 
@@ -57,6 +63,8 @@ def lib():
         _lib = ctypes.CDLL(_LIB_PATH)
         _lib.b200emb_workspace_bytes.restype = ctypes.c_size_t
         _lib.b200emb_workspace_bytes.argtypes = [ctypes.c_int64] * 3
+        _lib.b200emb_shard_block.restype = ctypes.c_void_p
+        _lib.b200emb_shard_status_ptr.restype = ctypes.c_void_p
     return _lib
 
 
@@ -527,3 +535,111 @@ def merge_ids(x, shard_num, workspace, out=None):
     _check(fn(_ptr(x), ctypes.c_int64(n), ctypes.c_int64(d), ctypes.c_int64(shard_num), _ptr(workspace),
               ctypes.c_size_t(workspace.numel()), _ptr(out), _stream()), "merge_ids")
     return out
+
+
+# ---------------------------------------------------------------- row-sharded step engine (b200emb_shard_*)
+def _view(ptr, n, dtype, device):
+    """torch view of n elements of device memory owned by the library."""
+    typestr = {torch.float32: "<f4", torch.int64: "<i8", torch.int32: "<i4", torch.uint8: "|u1"}[dtype]
+
+    class _Iface:
+        pass
+    o = _Iface()
+    o.__cuda_array_interface__ = {"shape": (int(n),), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+    return torch.as_tensor(o, device=device)
+
+
+class ShardEngine:
+    """One rank of the row-sharded table (include/b200emb.h, b200emb_shard_*): owner(id) = id % world.
+    `shard` [ceil(height/world), d] float32 (and moments for Adam) stay owned by the caller.  After
+    construction exchange `handle` between the ranks and call connect(all_handles); ranks hosted in one
+    process use connect_local(engines) instead."""
+
+    SGD, ADAM = 0, 1
+
+    def __init__(self, world, rank, height, d, shard, max_ids, max_recv, optimizer="sgd", m1=None, m2=None):
+        _need_cuda(shard, m1, m2)
+        assert shard.dtype == torch.float32 and shard.is_contiguous()
+        self.world, self.rank, self.height, self.d = int(world), int(rank), int(height), int(d)
+        self.device = shard.device
+        self.shard, self.m1, self.m2 = shard, m1, m2
+        self.h = ctypes.c_void_p()
+        opt = self.ADAM if optimizer == "adam" else self.SGD
+        with torch.cuda.device(self.device):
+            _check(lib().b200emb_shard_create(
+                ctypes.c_int(world), ctypes.c_int(rank), ctypes.c_int64(height), ctypes.c_int64(d), ctypes.c_int(opt),
+                _ptr(shard), _ptr(m1), _ptr(m2), ctypes.c_int64(max_ids), ctypes.c_int64(max_recv),
+                ctypes.byref(self.h)), "shard_create")
+            hb = (ctypes.c_ubyte * 64)()
+            _check(lib().b200emb_shard_export(self.h, hb), "shard_export")
+        self.handle = bytes(hb)
+        self.block = int(lib().b200emb_shard_block(self.h))
+        info = (ctypes.c_int64 * 8)()
+        _check(lib().b200emb_shard_info(self.h, info), "shard_info")
+        self.hs, self.plan_h, self.cap_ids, self.cap_src, self.cap_recv, self.block_bytes = (int(info[i]) for i in range(2, 8))
+        self.status = _view(lib().b200emb_shard_status_ptr(self.h), 1, torch.int32, self.device)
+        self._n = [0] * 4
+        self._keep = [None] * 4
+
+    def connect(self, handles):
+        buf = (ctypes.c_ubyte * (64 * self.world)).from_buffer_copy(b"".join(handles))
+        with torch.cuda.device(self.device):
+            _check(lib().b200emb_shard_connect(self.h, buf), "shard_connect")
+
+    @staticmethod
+    def connect_local(engines):
+        """Ranks living in this process (one or several GPUs with peer access): hand every engine all blocks."""
+        blocks = (ctypes.c_void_p * len(engines))(*[e.block for e in engines])
+        for e in engines:
+            with torch.cuda.device(e.device):
+                _check(lib().b200emb_shard_connect_ptrs(e.h, blocks), "shard_connect_ptrs")
+
+    def prepare(self, slot, ids, stream=None):
+        _need_cuda(ids)
+        assert ids.dtype == torch.int64 and ids.is_contiguous()
+        self._n[slot] = ids.numel()
+        self._keep[slot] = ids
+        _check(lib().b200emb_shard_prepare(self.h, ctypes.c_int(slot), _ptr(ids), ctypes.c_int64(ids.numel()),
+                                           _stream(stream)), "shard_prepare")
+
+    def lookup(self, slot, out=None, stream=None, phases=None):
+        if out is None:
+            out = torch.empty((self._n[slot], self.d), dtype=torch.float32, device=self.device)
+        if phases is None:
+            _check(lib().b200emb_shard_lookup(self.h, ctypes.c_int(slot), _ptr(out), _stream(stream)), "shard_lookup")
+        else:
+            _check(lib().b200emb_shard_lookup_phases(self.h, ctypes.c_int(slot), _ptr(out), _stream(stream),
+                                                     ctypes.c_int(phases[0]), ctypes.c_int(phases[1])), "shard_lookup_phases")
+        return out
+
+    def update(self, slot, d_out, lr, b1p=None, b2p=None, beta1=0.9, beta2=0.999, eps=1e-8, stream=None, phases=None):
+        _need_cuda(d_out, lr, b1p, b2p)
+        args = (self.h, ctypes.c_int(slot), _ptr(d_out), _ptr(lr), _ptr(b1p), _ptr(b2p), ctypes.c_float(beta1),
+                ctypes.c_float(beta2), ctypes.c_float(eps), _stream(stream))
+        if phases is None:
+            _check(lib().b200emb_shard_update(*args), "shard_update")
+        else:
+            _check(lib().b200emb_shard_update_phases(*args, ctypes.c_int(phases[0]), ctypes.c_int(phases[1])),
+                   "shard_update_phases")
+
+    def debug_views(self, slot):
+        """(split points [world+1], unique count [1], owner segment starts [world+1], step counter) as device views."""
+        out = (ctypes.c_void_p * 6)()
+        _check(lib().b200emb_shard_debug_ptrs(self.h, ctypes.c_int(slot), out), "shard_debug_ptrs")
+        w = self.world
+        return (_view(out[0], w + 1, torch.int64, self.device), _view(out[1], 1, torch.int64, self.device),
+                _view(out[2], w + 1, torch.int64, self.device), _view(out[4], 1, torch.int64, self.device))
+
+    def check_status(self):
+        """Raise if a kernel of the sharded step flagged a time-out or a capacity overflow (reads the device word)."""
+        st = int(self.status.item())
+        if st & STATUS_BARRIER_TIMEOUT:
+            raise B200EmbError("sharded step: a rank did not arrive within 20 s (status %d)" % st)
+        if st & STATUS_SHARD_OVERFLOW:
+            raise B200EmbError("sharded step: more rows than the capacities given at create() (status %d)" % st)
+        return st
+
+    def destroy(self):
+        if self.h:
+            lib().b200emb_shard_destroy(self.h)
+            self.h = ctypes.c_void_p()

@@ -116,6 +116,29 @@ __device__ __forceinline__ uint32_t match_digit(uint32_t digit, bool valid) {
 }
 
 // ---------------------------------------------------------------------------
+// Consumer side of the sharded path's arrival flags (WaitSpec, internal.h); call with the whole CTA.
+__device__ __forceinline__ void wait_for_flags(const unsigned long long* flags, const unsigned long long* epoch,
+                                               int world, int32_t* status) {
+  if (flags == nullptr) return;
+  if (static_cast<int>(threadIdx.x) < world) {
+    const unsigned long long want = *reinterpret_cast<const volatile unsigned long long*>(epoch);
+    unsigned long long t0, t, v;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (;;) {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(flags + threadIdx.x) : "memory");
+      if (v >= want) break;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      if (t - t0 > 20000000000ull) {   // 20 s: a rank is gone; do not hang the device
+        if (status) atomicOr(status, 4);
+        break;
+      }
+      __nanosleep(64);
+    }
+  }
+  __syncthreads();
+}
+
+// ---------------------------------------------------------------------------
 // Row-shape dispatch: picks (LPR, NV, VEC) from D and pointer alignment and calls
 // f.template operator()<LPR, NV, VEC>().
 template <typename T, class F>

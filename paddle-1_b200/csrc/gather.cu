@@ -24,6 +24,7 @@ __global__ void __launch_bounds__(kBlock, 4)
 k_gather(const T* __restrict__ table, const int64_t* __restrict__ ids, T* __restrict__ out,
          int64_t n, int64_t height, int d, int64_t padding_idx, int32_t* status,
          const int64_t* __restrict__ seg_start, T* const* __restrict__ seg_dst, int segs) {
+  if (segs > 0) n = min(n, seg_start[segs]);   // sharded owner side: the live count exists on the device only
   constexpr int EPV = Epv<T, VEC>::value;
   constexpr int kGroups = kBlock / LPR;
   const int l = threadIdx.x % LPR;

@@ -98,6 +98,16 @@ cudaError_t launch_cluster_sort(const int64_t* rows, int64_t n, int64_t height, 
                                 uint32_t* keys_out, uint32_t* perm_out, int32_t* status,
                                 cudaStream_t s);
 
+// Optional wait at the start of a consumer kernel of the sharded path: the first `world` threads of every CTA
+// spin (ld.acquire.sys) until flags[r] >= *epoch for every source rank r — the data those ranks stored into
+// this GPU's buffers before raising their flag is then visible to the whole CTA.  flags == nullptr: no wait.
+struct WaitSpec {
+  const unsigned long long* flags = nullptr;   // [world], written by the peers (st.release.sys)
+  const unsigned long long* epoch = nullptr;   // device word: the step being waited for
+  int world = 0;
+  int32_t* status = nullptr;                   // B200EMB_STATUS_BARRIER_TIMEOUT after ~20 s
+};
+
 // gather.cu
 // `seg_start`/`seg_dst` (device arrays, `segs` entries + 1 / `segs` entries) optionally scatter the output:
 // row k of segment g (seg_start[g] <= k < seg_start[g+1]) is stored at seg_dst[g] + (k - seg_start[g]) * d.
@@ -105,6 +115,7 @@ template <typename T>
 cudaError_t launch_gather(const T* table, int64_t height, int64_t d, const int64_t* ids, int64_t n,
                           int64_t padding_idx, T* out, int32_t* status, cudaStream_t s,
                           const int64_t* seg_start = nullptr, T* const* seg_dst = nullptr, int segs = 0);
+// with a scatter map only the first seg_start[segs] ids are looked up (a count known on the device alone)
 
 // segreduce.cu
 enum class UpdateOp { kMergeAdd, kAddToTensor, kSgd, kAdam, kAdagrad };
@@ -119,9 +130,11 @@ struct UpdateArgs {
   const T* beta2_pow = nullptr;
   T beta1 = 0, beta2 = 0, epsilon = 0;
   const uint32_t* uidx = nullptr;  // kMergeAdd: sorted position -> output row
-  const int64_t* shard_bounds = nullptr;   // kMergeAdd scatter map (device arrays), see segreduce.cu Params
+  const int64_t* shard_bounds = nullptr;   // kMergeAdd scatter map (device arrays), see segreduce.cuh Params
   T* const* shard_dst = nullptr;
+  const int64_t* shard_meta = nullptr;     // optional device pairs {row offset inside the destination, rows it accepts}
   int shards = 0;
+  WaitSpec wait;                           // sharded path: the gradient rows come from other GPUs
   bool dst_aligned16 = true;               // caller's promise about the scatter destinations
 };
 template <typename T>
@@ -143,6 +156,6 @@ cudaError_t launch_segment_scatter_i64(const int64_t* src, int64_t n_upper, cons
 // mode 0: out[e] = src[perm[e]]   1: out[perm[e]] = src[uidx[e]]   2: out[perm[e]] = src[e]
 template <typename T>
 cudaError_t launch_permute_rows(const T* src, const SortedPlan& plan, const uint32_t* uidx, int64_t n,
-                                int64_t d, T* out, int mode, cudaStream_t s);
+                                int64_t d, T* out, int mode, cudaStream_t s, const WaitSpec& wait = WaitSpec());
 
 }  // namespace b200emb

@@ -1,4 +1,4 @@
-// segreduce.cu — duplicate-row reduction fused with the consumer (K3/K4/K5a/K5b), sm_100a.
+// segreduce.cuh — duplicate-row reduction fused with the consumer (K3/K4/K5a/K5b), sm_100a.
 //
 // Input: the sort plan (sorted ids + original positions) and the [N,D] gradient rows.
 // One skeleton, four consumers selected at compile time:
@@ -12,8 +12,12 @@
 //
 // FAST mode (k_chunk_reduce): the sorted element range is cut into equal chunks, one
 // per lane group, so work is balanced no matter how skewed the ids are (a Zipf head id owns
-// 10-25% of all rows).  A group walks its chunk with kBatch independent row loads in flight;
-// segments that close inside the chunk are consumed immediately.  Segments cut by a chunk
+// 10-25% of all rows).  A group walks its chunk through a shared-memory ring filled by cp.async
+// (LDGSTS): every lane copies ITS 16 bytes of each gradient row — and of the parameter / moment rows of
+// every segment that closes at that row — into slots only it reads back, so the ring needs no barrier at
+// all, only cp.async.wait_group; three batches are in flight while one is consumed (the loads of batch
+// k+3 are issued as soon as batch k has been added up), and no payload lives in registers.
+// Segments that close inside the chunk are consumed immediately.  Segments cut by a chunk
 // boundary leave partial sums in shared memory, are combined across the CTA's groups in fixed
 // order, and — if they also cross the CTA boundary — leave one carry row per CTA; the last CTA
 // of such a chain to finish (an integer arrival counter, nobody waits) sums the chain's carries in
@@ -24,7 +28,9 @@
 // order (the stable sort keeps it) with separately rounded IEEE operations, reproducing the
 // reference CPU loops bit for bit.  Its critical path is the longest duplicate run; it is the
 // parity mode, not the speed mode.
+#pragma once
 #include <algorithm>
+#include <atomic>
 #include <cstdlib>
 
 #include "common.cuh"
@@ -34,6 +40,21 @@ namespace b200emb {
 namespace {
 
 constexpr uint32_t kHead = 1u, kTail = 2u, kThrough = 4u;             // per-group flags
+
+// ---- developer trace (tools/ only: built with -DB200EMB_TRACE) -------------------------------------
+#ifdef B200EMB_TRACE
+__device__ unsigned long long g_trace[8192][8];
+#define B200EMB_STAMP(slot)                                                                   \
+  do {                                                                                        \
+    if (threadIdx.x == 0 && blockIdx.x < 8192) {                                              \
+      unsigned long long t_;                                                                  \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                  \
+      g_trace[blockIdx.x][slot] = t_;                                                         \
+    }                                                                                         \
+  } while (0)
+#else
+#define B200EMB_STAMP(slot) do {} while (0)
+#endif
 
 template <typename T>
 struct Params {
@@ -49,6 +70,8 @@ struct Params {
   const int64_t* shard_bounds;
   T* const* shard_dst;
   int shards;
+  const int64_t* shard_meta;  // optional pairs {rows to skip at the start of destination g, rows it accepts}
+  WaitSpec wait;              // sharded owner side: `value` is stored by other GPUs; wait for their flags first
 };
 
 template <typename T>
@@ -92,6 +115,24 @@ template <UpdateOp OP> struct NumState {
 template <typename T, UpdateOp OP, int NV, int EPV>
 struct RowState { T v[NumState<OP>::value == 0 ? 1 : NumState<OP>::value][NV][EPV]; };
 
+// ---- cp.async (LDGSTS) ring helpers ----------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_addr(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+// BYTES = 16: L2 only (.cg, streaming data); 4 / 8 (scalar path of odd widths): .ca is the only form
+template <int BYTES>
+__device__ __forceinline__ void cp_async(void* smem_dst, const void* gsrc) {
+  if constexpr (BYTES == 16)
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(smem_addr(smem_dst)), "l"(gsrc) : "memory");
+  else
+    asm volatile("cp.async.ca.shared.global [%0], [%1], %2;" :: "r"(smem_addr(smem_dst)), "l"(gsrc), "n"(BYTES) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
+
+constexpr int kBoundarySlack = 64;        // a CTA boundary moves forward by at most this many elements
+
 template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
 __device__ __forceinline__ void load_state(const Params<T>& P, uint32_t key, int col0, int l,
                                            RowState<T, OP, NV, Epv<T, VEC>::value>& st) {
@@ -128,7 +169,12 @@ __device__ __forceinline__ void apply_state(const Params<T>& P, uint32_t key, ui
     if (P.shards > 0) {
       int g = 0;
       while (g + 1 < P.shards && row >= P.shard_bounds[g + 1]) ++g;
-      merge_dst = P.shard_dst[g] + (row - P.shard_bounds[g]) * P.d;
+      int64_t k = row - P.shard_bounds[g];
+      if (P.shard_meta) {
+        if (k >= P.shard_meta[2 * g + 1]) return;   // the owner ran out of room (it raised the overflow status bit)
+        k += P.shard_meta[2 * g];
+      }
+      merge_dst = P.shard_dst[g] + k * P.d;
     }
   }
 #pragma unroll
@@ -186,13 +232,6 @@ __device__ __forceinline__ void consume(const Params<T>& P, uint32_t key, uint32
   load_state<T, OP, LPR, NV, VEC>(P, key, col0, l, st);
   apply_state<T, OP, LPR, NV, VEC>(P, key, eref, col0, l, acc, st);
 }
-
-// Resident CTAs per SM the register allocation aims for.  The MergeAdd consumer keeps no state rows in
-// registers and fits 80 registers without spilling, so it runs 3 CTAs per SM (measured: the sharded
-// path's local MergeAdd 6 % faster); the optimizer consumers spill at that size and lose (C3 +9 %), so they
-// keep 128 registers and 2 CTAs.
-template <UpdateOp OP, int NV>
-constexpr int chunk_min_ctas() { return (OP == UpdateOp::kMergeAdd && NV <= 2) ? 3 : 2; }
 
 // Closes one chain: the segment that leaves CTA `c` (tail carry) and enters the next `len` CTAs
 // (head carries).  Run by the LAST CTA of the chain to arrive, with the whole CTA: the lane
@@ -269,38 +308,118 @@ __device__ __forceinline__ void close_chain(int c, int len, uint32_t key, uint32
 }
 
 // ------------------------------------------------------------------------------------------
+// Geometry of one launch, fixed by (N, D) alone (never by the consumer): `chunk` sorted elements per lane
+// group nominally, CTA c nominally owns [c*stride, (c+1)*stride) with stride = groups*chunk.  A nominal
+// boundary that falls inside a segment is moved FORWARD to that segment's end when the end is at most
+// `slack` elements away, so only segments longer than that (the Zipf head) are ever shared between CTAs;
+// a CTA then splits its adjusted range evenly over its groups.
+struct ChunkGeom {
+  int n, chunk, slack;
+};
+
+// Rows per batch of the shared-memory ring (kRingStages batches in flight): sized so that the ring of a
+// CTA stays near 48 KB and three CTAs fit an SM for the common shapes.
+constexpr int kRingStages = 3;
+template <typename T, UpdateOp OP, int NV, bool VEC>
+struct Ring {
+  static constexpr int kVB = Epv<T, VEC>::value * static_cast<int>(sizeof(T));   // bytes per lane per vector
+  static constexpr int kParts = 1 + NumState<OP>::value;                         // gradient row + state rows
+  static constexpr int kSlotBytes = kParts * NV * kVB * kBlock;                  // one slot, whole CTA
+  static constexpr int kFit = (48 * 1024) / (kRingStages * kSlotBytes);
+  static constexpr int kBatch = kFit >= 4 ? 4 : (kFit >= 2 ? 2 : 1);
+  // one more slot holds the state of the segment a group leaves open (single-state consumers only: for
+  // Adam / Adagrad that slot would cost a resident CTA)
+  static constexpr bool kTailInRing = NumState<OP>::value == 1;
+  static constexpr int kSlots = kRingStages * kBatch + (kTailInRing ? 1 : 0);
+  static constexpr int kBytes = kSlots * kSlotBytes;
+};
+
+__device__ __forceinline__ void lds_vec(uint32_t addr, float (&v)[4]) {
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]) : "r"(addr));
+}
+__device__ __forceinline__ void lds_vec(uint32_t addr, double (&v)[2]) {
+  asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(v[0]), "=d"(v[1]) : "r"(addr));
+}
+__device__ __forceinline__ void lds_vec(uint32_t addr, float (&v)[1]) {
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v[0]) : "r"(addr));
+}
+__device__ __forceinline__ void lds_vec(uint32_t addr, double (&v)[1]) {
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v[0]) : "r"(addr));
+}
+template <int BYTES>
+__device__ __forceinline__ void cp_async_s(uint32_t smem_dst, const void* gsrc) {
+  if constexpr (BYTES == 16)
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(smem_dst), "l"(gsrc) : "memory");
+  else
+    asm volatile("cp.async.ca.shared.global [%0], [%1], %2;" :: "r"(smem_dst), "l"(gsrc), "n"(BYTES) : "memory");
+}
+
+constexpr uint32_t kPosMask = 0x3FFFFFFFu;   // N < 2^30: the two top bits of a staged position carry flags
+constexpr uint32_t kCloses = 0x80000000u;    // the segment ends at this element
+constexpr uint32_t kDirect = 0x40000000u;    // ... and started inside this group's chunk: consumed on the spot
+
 template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
-__global__ void __launch_bounds__(kBlock, chunk_min_ctas<OP, NV>())
-k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ perm, int n,
-               int chunk, const T* __restrict__ value, Params<T> P, Carry<T> C) {
+__global__ void __launch_bounds__(kBlock, NV == 1 ? 3 : 2)
+k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ perm, ChunkGeom G,
+               const T* __restrict__ value, Params<T> P, Carry<T> C) {
   constexpr int EPV = Epv<T, VEC>::value;
   constexpr int GPC = kBlock / LPR;
   constexpr int COLS = LPR * NV * EPV;
-  // gradient rows (+ the state rows of segments closing among them) in flight per group
-  constexpr int kBatch = NV == 1 ? (NumState<OP>::value <= 1 ? 8 : 4) : (NV == 2 ? 4 : 2);
+  constexpr int NS = NumState<OP>::value;
+  using RG = Ring<T, OP, NV, VEC>;
+  constexpr int VB = RG::kVB, B = RG::kBatch, S = kRingStages;
+  constexpr uint32_t kVecStride = kBlock * VB;                 // between the vectors of one slot
+  constexpr uint32_t kPartStride = NV * kVecStride;            // between the parts (row, state rows) of one slot
+  constexpr uint32_t kSlotStride = RG::kSlotBytes;
+  constexpr int kTailSlot = S * B;                             // state of the segment a group leaves open
   using A = Arith<T>;
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  T* s_head = reinterpret_cast<T*>(smem_raw);                 // [GPC][COLS]
-  T* s_tail = s_head + GPC * COLS;                            // [GPC][COLS]
-  uint32_t* s_key = reinterpret_cast<uint32_t*>(s_tail + GPC * COLS);  // [GPC*chunk]
-  uint32_t* s_perm = s_key + GPC * chunk;
-  __shared__ uint32_t s_flags[GPC];
-  __shared__ uint32_t s_prev_key, s_next_key;
-  __shared__ int s_before, s_after, s_nfix, s_fix_c[2], s_fix_len[2];
-
+  const int n = G.n;
+  const int stride = GPC * G.chunk;                            // nominal sorted elements per CTA
+  const int win = stride + G.slack + 2;                        // staged key window
   const int tid = threadIdx.x, g = tid / LPR, l = tid % LPR;
+  const int lane = tid & 31, warp = tid >> 5;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  // ring[slot][part][vector][thread], filled by cp.async: a thread only ever touches its own column, so the
+  // ring needs no barrier, only cp.async.wait_group
+  const uint32_t ring = smem_addr(smem_raw) + tid * VB;
+  T* s_head = reinterpret_cast<T*>(smem_raw + RG::kBytes);    // [GPC][COLS]
+  T* s_tail = s_head + GPC * COLS;                            // [GPC][COLS]
+  uint32_t* s_key = reinterpret_cast<uint32_t*>(s_tail + GPC * COLS);  // [win]
+  uint32_t* s_pos = s_key + win;                              // [win] original position | kCloses | kDirect
+  __shared__ uint32_t s_flags[GPC];
+  __shared__ int s_a, s_b, s_before, s_after, s_nfix, s_fix_c[2], s_fix_len[2];
+
+  const int cta = blockIdx.x, num_ctas = gridDim.x;
   const int d = P.d;
-  const int cta_start = blockIdx.x * GPC * chunk;
-  const int cta_count = min(GPC * chunk, n - cta_start);
-  for (int i = tid; i < cta_count; i += kBlock) {
-    s_key[i] = skey[cta_start + i];
-    s_perm[i] = perm[cta_start + i];
-  }
-  if (tid == 0) {
-    s_prev_key = cta_start > 0 ? skey[cta_start - 1] : kNoKey;
-    s_next_key = cta_start + cta_count < n ? skey[cta_start + cta_count] : kNoKey;
+  wait_for_flags(P.wait.flags, P.wait.epoch, P.wait.world, P.wait.status);
+  const int nom_s = cta * stride, nom_e = min(nom_s + stride, n);
+  const int w0 = max(nom_s - 1, 0), w1 = min(nom_e + G.slack + 1, n);
+  B200EMB_STAMP(0);
+  for (int i = w0 + tid; i < w1; i += kBlock) {
+    s_key[i - w0] = skey[i];
+    s_pos[i - w0] = perm[i];
   }
   __syncthreads();
+  const auto K = [&](int i) { return s_key[i - w0]; };          // w0 <= i < w1
+  // adjusted boundary of nominal position p (the CTAs on both sides of it compute the same value)
+  if (warp < 2) {
+    const int p = warp == 0 ? nom_s : nom_e;
+    int adj = p;
+    if (p > 0 && p < n && K(p) == K(p - 1)) {
+      const int hi = min(p + G.slack, n - 1);
+      for (int q0 = p + 1; q0 <= hi; q0 += 32) {
+        const int q = q0 + lane;
+        const bool brk = q <= hi && K(q) != K(q - 1);
+        const uint32_t m = __ballot_sync(0xffffffffu, brk);
+        if (m) { adj = q0 + __ffs(m) - 1; break; }
+      }
+    }
+    if (lane == 0) { if (warp == 0) s_a = adj; else s_b = adj; }
+  }
+  __syncthreads();
+  const int a = s_a, b = s_b;                                   // this CTA reduces sorted positions [a, b)
+  const uint32_t prev_key = a > 0 ? K(a - 1) : kNoKey;
+  const uint32_t next_key = b < n ? K(b) : kNoKey;
 
   // ---- chains: segments cut by CTA boundaries, known from the keys alone ------------------------
   // A chain is one segment spread over consecutive CTAs: it LEAVES the CTA where it starts (tail
@@ -308,78 +427,143 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
   // arrive[first CTA of the chain]; the member that arrives last closes the chain (close_chain).
   // No CTA ever waits for another one.  The chain's extent is found by probing the sorted keys at
   // the CTA boundaries: the first 32 probes are issued here and only read after the main loop.
-  const int lane = tid & 31, warp = tid >> 5;
-  const int cta = blockIdx.x, num_ctas = gridDim.x;
-  const int64_t stride = static_cast<int64_t>(GPC) * chunk;          // sorted elements per CTA
-  const uint32_t k_first = s_key[0], k_last = s_key[cta_count - 1];
-  const bool has_head = s_prev_key == k_first;                        // a segment enters from CTA cta-1
-  const bool through = has_head && k_last == k_first && s_next_key == k_first;   // ... and runs on past this CTA
-  const bool has_tail = !through && s_next_key == k_last;             // a segment that starts here leaves
-  // enters(j): the chain's segment enters CTA j from CTA j-1;   member(j): CTA j starts inside it
-  const auto enters = [&](int j) { return j >= 1 && __ldg(skey + j * stride - 1) == k_first; };
+  const uint32_t k_first = K(a), k_last = K(b - 1);
+  // Out-of-range rows (key == height: flagged by the plan, and the padding of the sharded owner side) sort
+  // last and are never applied: a CTA that holds nothing else is done, and they never form a chain.
+  if (k_first >= P.height) return;
+  const bool has_head = prev_key == k_first;                          // a segment enters from CTA cta-1
+  const bool through = has_head && k_last == k_first && next_key == k_first;   // ... and runs on past this CTA
+  const bool has_tail = !through && next_key == k_last && k_last < P.height;   // a segment that starts here leaves
+  // cut(j, k): the boundary before CTA j stayed inside a segment of key k (it was not moved): the keys
+  // from position j*stride-1 to `slack` elements further on are all k
+  const auto cut = [&](int j, uint32_t k) {
+    const int64_t p = static_cast<int64_t>(j) * stride;
+    return __ldg(skey + p - 1) == k && __ldg(skey + min(p + G.slack, static_cast<int64_t>(n) - 1)) == k;
+  };
+  const auto enters = [&](int j) { return j >= 1 && cut(j, k_first); };     // the chain enters CTA j from j-1
   const uint32_t k_fwd = through ? k_first : k_last;
-  const auto member = [&](int j) { return j < num_ctas && __ldg(skey + j * stride) == k_fwd; };
+  const auto member = [&](int j) { return j < num_ctas && cut(j, k_fwd); }; // CTA j starts inside the chain
   bool probe = false;
   if (warp == 0 && has_head) probe = enters(cta - 1 - lane);
   if (warp == 1 && (through || has_tail)) probe = member(cta + 1 + lane);
 
-  const int gs = g * chunk;
-  const int ge = min(gs + chunk, cta_count);
-  const bool active = gs < cta_count;
+  const int chunk_c = (b - a + GPC - 1) / GPC;                  // this CTA's elements per group
+  const int ngroups = (b - a + chunk_c - 1) / chunk_c;          // groups that own elements
+  const int gs = a + g * chunk_c;
+  const int ge = min(gs + chunk_c, b);
+  const bool active = g < ngroups;
+  uint32_t prev = kNoKey, next = kNoKey, kf = 0, last = 0;
+  bool enters_chunk = false, open_tail = false;
+  if (active) {
+    prev = gs > a ? K(gs - 1) : prev_key;
+    next = ge < b ? K(ge) : next_key;
+    kf = K(gs);
+    last = K(ge - 1);
+    enters_chunk = kf == prev;                                  // the chunk starts inside a segment begun before it
+    open_tail = last == next && !(enters_chunk && last == kf);  // a segment starts in this chunk and runs on
+    // per-element flags, from the keys alone: where segments end, and whether they began in this chunk
+    for (int idx = gs + l; idx < ge; idx += LPR) {
+      const uint32_t key = K(idx);
+      const uint32_t kn = idx + 1 < ge ? K(idx + 1) : next;
+      uint32_t f = 0;
+      if (key != kn) f = kCloses | ((enters_chunk && key == kf) ? 0u : kDirect);
+      s_pos[idx - w0] |= f;
+    }
+  }
+  __syncwarp();       // a group lives inside one warp
+  B200EMB_STAMP(1);
+  const int nbatch = active ? (ge - gs + B - 1) / B : 0;
 
   for (int col0 = 0; col0 < d; col0 += COLS) {
     uint32_t flags = 0, tail_key = 0, tail_eref = 0;
     if (active) {
-      const uint32_t prev = gs > 0 ? s_key[gs - 1] : s_prev_key;
-      const uint32_t next = ge < cta_count ? s_key[ge] : s_next_key;
-      bool first = true;   // no segment has closed inside this chunk yet
-      T acc[NV][EPV];
-      zero_acc<T, NV, EPV>(acc);
-      for (int e0 = gs; e0 < ge; e0 += kBatch) {
-        // Everything about segment structure comes from the keys already in shared memory, so the
-        // batch's gradient rows AND the state rows of every segment that closes inside it are
-        // requested together: one round trip per batch.
-        uint32_t k[kBatch];
-        bool in[kBatch], closes[kBatch], direct[kBatch];
-        bool f = first;
-#pragma unroll
-        for (int b = 0; b < kBatch; ++b) {
-          const int idx = e0 + b;
-          in[b] = idx < ge;
-          k[b] = in[b] ? s_key[idx] : kNoKey;
-          const uint32_t kn = (idx + 1 < ge) ? s_key[idx + 1] : next;
-          closes[b] = in[b] && k[b] != kn;
-          direct[b] = closes[b] && !(f && k[b] == prev);
-          f = f && !closes[b];
-        }
-        T r[kBatch][NV][EPV];
-        RowState<T, OP, NV, EPV> st[kBatch];
-#pragma unroll
-        for (int b = 0; b < kBatch; ++b) {
-          const int idx = e0 + b;
-          const int64_t src = in[b] ? static_cast<int64_t>(s_perm[idx]) * d : 0;
+      // state rows of a key into ring slot `slot` (parts 1..NS)
+      const auto fetch_state = [&](uint32_t slot_addr, uint32_t key) {
+        if constexpr (NS > 0) {
+          if (key >= P.height) return;
+          const int64_t base = static_cast<int64_t>(key) * d;
 #pragma unroll
           for (int kk = 0; kk < NV; ++kk) {
             const int col = col0 + (l + kk * LPR) * EPV;
-            if (in[b] && col < d) load_vec_stream<T, VEC>(value + src + col, r[b][kk]);
-            else {
-#pragma unroll
-              for (int e = 0; e < EPV; ++e) r[b][kk][e] = T(0);
+            if (col >= d) continue;
+            const uint32_t dst = slot_addr + kPartStride + kk * kVecStride;
+            cp_async_s<VB>(dst, P.param + base + col);
+            if constexpr (OP == UpdateOp::kAdam) {
+              cp_async_s<VB>(dst + kPartStride, P.m1 + base + col);
+              cp_async_s<VB>(dst + 2 * kPartStride, P.m2 + base + col);
             }
+            if constexpr (OP == UpdateOp::kAdagrad) cp_async_s<VB>(dst + kPartStride, P.m1 + base + col);
           }
-          if (direct[b]) load_state<T, OP, LPR, NV, VEC>(P, k[b], col0, l, st[b]);
         }
+      };
+      const auto read_state = [&](uint32_t slot_addr, uint32_t key, RowState<T, OP, NV, EPV>& st) {
+        if constexpr (NS > 0) {
+          if (key >= P.height) return;
 #pragma unroll
-        for (int b = 0; b < kBatch; ++b) {
-          if (in[b]) {
+          for (int q = 0; q < NS; ++q)
 #pragma unroll
-            for (int kk = 0; kk < NV; ++kk)
+            for (int kk = 0; kk < NV; ++kk) {
+              const int col = col0 + (l + kk * LPR) * EPV;
+              if (col < d) lds_vec(slot_addr + (1 + q) * kPartStride + kk * kVecStride, st.v[q][kk]);
+            }
+        }
+      };
+      // Everything about a batch is known from the staged keys, so the state rows of every segment that
+      // closes in it are requested together with its gradient rows, kRingStages batches ahead.
+      const auto request = [&](int bi) {
+        const int i0 = gs + bi * B;
+        const uint32_t stage_addr = ring + (bi % S) * (B * kSlotStride);
 #pragma unroll
-              for (int e = 0; e < EPV; ++e) acc[kk][e] = A::add(acc[kk][e], r[b][kk][e]);
-            if (closes[b]) {
-              if (direct[b]) {
-                apply_state<T, OP, LPR, NV, VEC>(P, k[b], static_cast<uint32_t>(cta_start + e0 + b),
-                                                 col0, l, acc, st[b]);
+        for (int q = 0; q < B; ++q) {
+          const int idx = i0 + q;
+          if (idx < ge) {
+            const uint32_t pw = s_pos[idx - w0];
+            const T* src = value + static_cast<int64_t>(pw & kPosMask) * d;
+            const uint32_t slot_addr = stage_addr + q * kSlotStride;
+#pragma unroll
+            for (int kk = 0; kk < NV; ++kk) {
+              const int col = col0 + (l + kk * LPR) * EPV;
+              if (col < d) cp_async_s<VB>(slot_addr + kk * kVecStride, src + col);
+            }
+            if (NS > 0 && (pw & kDirect)) fetch_state(slot_addr, K(idx));
+          }
+        }
+      };
+      if (RG::kTailInRing && open_tail) fetch_state(ring + kTailSlot * kSlotStride, last);   // joins the first group
+#pragma unroll
+      for (int s = 0; s < S; ++s) {   // empty groups keep the wait arithmetic uniform
+        if (s < nbatch) request(s);
+        cp_async_commit();
+      }
+      bool first = true;   // no segment has closed inside this chunk yet
+      T acc[NV][EPV];
+      zero_acc<T, NV, EPV>(acc);
+      for (int bi = 0; bi < nbatch; ++bi) {
+        cp_async_wait<S - 1>();       // batch bi has landed (this thread's own copies)
+        const int i0 = gs + bi * B;
+        const uint32_t stage_addr = ring + (bi % S) * (B * kSlotStride);
+#pragma unroll
+        for (int q = 0; q < B; ++q) {
+          const int idx = i0 + q;
+          if (idx < ge) {
+            const uint32_t slot_addr = stage_addr + q * kSlotStride;
+#pragma unroll
+            for (int kk = 0; kk < NV; ++kk) {
+              const int col = col0 + (l + kk * LPR) * EPV;
+              if (col < d) {
+                T r[EPV];
+                lds_vec(slot_addr + kk * kVecStride, r);
+#pragma unroll
+                for (int e = 0; e < EPV; ++e) acc[kk][e] = A::add(acc[kk][e], r[e]);
+              }
+            }
+            const uint32_t pw = s_pos[idx - w0];
+            if (pw & kCloses) {   // the segment closes here
+              if (pw & kDirect) {
+                const uint32_t key = K(idx);
+                RowState<T, OP, NV, EPV> st;
+                read_state(slot_addr, key, st);
+                apply_state<T, OP, LPR, NV, VEC>(P, key, static_cast<uint32_t>(idx), col0, l, acc, st);
               } else {  // first segment of the chunk, entered from the previous chunk
 #pragma unroll
                 for (int kk = 0; kk < NV; ++kk)
@@ -392,8 +576,11 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
             }
           }
         }
+        if (bi + S < nbatch) request(bi + S);   // refill the stage just drained
+        cp_async_commit();
       }
-      const uint32_t last = s_key[ge - 1];
+      cp_async_wait<0>();
+      B200EMB_STAMP(2);
       if (last == next) {  // the chunk ends inside a segment: leave a partial sum
         const bool left_open = first && last == prev;
         T* dst = (left_open ? s_head : s_tail) + g * COLS;
@@ -406,12 +593,13 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
         } else {
           flags |= kTail;
           tail_key = last;
-          tail_eref = static_cast<uint32_t>(cta_start + ge - 1);
+          tail_eref = static_cast<uint32_t>(ge - 1);
         }
       }
     }
     if (l == 0) s_flags[g] = flags;
     __syncthreads();
+    B200EMB_STAMP(3);
 
     // ---- combine partial segments across the CTA's groups, in group order -----------------
     if (active && (flags & kTail)) {
@@ -422,7 +610,7 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
         for (int e = 0; e < EPV; ++e) sum[k][e] = s_tail[g * COLS + (l + k * LPR) * EPV + e];
       int j = g + 1;
       bool to_end = true;
-      while (j < GPC) {
+      while (j < ngroups) {
         const uint32_t f = s_flags[j];
         if (!(f & kHead)) { to_end = false; break; }
 #pragma unroll
@@ -439,6 +627,18 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
           const int col = col0 + (l + k * LPR) * EPV;
           if (col < d) store_vec<T, VEC>(C.tail + static_cast<int64_t>(blockIdx.x) * d + col, sum[k]);
         }
+      } else if constexpr (RG::kTailInRing) {   // its state rows were requested before the main loop
+        RowState<T, OP, NV, EPV> st;
+        if (tail_key < P.height) {
+#pragma unroll
+          for (int q = 0; q < NS; ++q)
+#pragma unroll
+            for (int kk = 0; kk < NV; ++kk) {
+              const int col = col0 + (l + kk * LPR) * EPV;
+              if (col < d) lds_vec(ring + kTailSlot * kSlotStride + (1 + q) * kPartStride + kk * kVecStride, st.v[q][kk]);
+            }
+        }
+        apply_state<T, OP, LPR, NV, VEC>(P, tail_key, tail_eref, col0, l, sum, st);
       } else {
         consume<T, OP, LPR, NV, VEC>(P, tail_key, tail_eref, col0, l, sum);
       }
@@ -451,7 +651,7 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
         for (int e = 0; e < EPV; ++e) sum[k][e] = s_head[(l + k * LPR) * EPV + e];
       bool to_end = (flags & kThrough) != 0;
       int j = 1;
-      while (to_end && j < GPC) {
+      while (to_end && j < ngroups) {
         const uint32_t f = s_flags[j];
         if (!(f & kHead)) { to_end = false; break; }
 #pragma unroll
@@ -470,6 +670,7 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
     }
     __syncthreads();
   }
+  B200EMB_STAMP(4);
   if (num_ctas == 1) return;
 
   // ---- arrivals -----------------------------------------------------------------------------------
@@ -511,16 +712,17 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
   }
   __syncthreads();
   const int nfix = s_nfix;
+  B200EMB_STAMP(5);
   if (nfix == 0) return;
   __threadfence();                       // the other members' carry rows, published before their arrivals
   for (int f = 0; f < nfix; ++f) {
     const int c0 = s_fix_c[f];
     const bool own_tail = c0 == cta;     // the chain that starts here; otherwise the one that entered
     close_chain<T, OP, LPR, NV, VEC>(c0, s_fix_len[f], own_tail ? k_last : k_first,
-                                     static_cast<uint32_t>(own_tail ? cta_start + cta_count - 1 : cta_start),
-                                     P, C, s_head);
+                                     static_cast<uint32_t>(own_tail ? b - 1 : a), P, C, s_head);
     if (tid == 0) C.arrive[c0] = 0;      // ready for the next launch on this workspace
   }
+  B200EMB_STAMP(6);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -537,6 +739,7 @@ k_segment_det(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ pe
   using A = Arith<T>;
   const int l = threadIdx.x % LPR;
   const int d = P.d;
+  wait_for_flags(P.wait.flags, P.wait.epoch, P.wait.world, P.wait.status);
   const int n_unique = static_cast<int>(hdr->n_unique);
   for (int s = blockIdx.x * GPC + threadIdx.x / LPR; s < n_unique; s += gridDim.x * GPC) {
     const int b = static_cast<int>(seg_start[s]);
@@ -613,7 +816,7 @@ cudaError_t launch_op(const SortedPlan& plan, const T* value, int64_t n, int64_t
                       cudaStream_t s) {
   Params<T> P{a.param, a.moment1, a.moment2, a.lr, a.beta1_pow, a.beta2_pow,
               a.beta1, a.beta2, a.epsilon, a.uidx, static_cast<int>(d),
-              static_cast<uint32_t>(height), a.shard_bounds, a.shard_dst, a.shards};
+              static_cast<uint32_t>(height), a.shard_bounds, a.shard_dst, a.shards, a.shard_meta, a.wait};
   Carry<T> C{reinterpret_cast<uint32_t*>(ws + L.off_cta_arrive),
              reinterpret_cast<T*>(ws + L.off_cta_head), reinterpret_cast<T*>(ws + L.off_cta_tail)};
   bool aligned = is_aligned16(value) && (a.shards > 0 || is_aligned16(a.param)) && a.dst_aligned16;
@@ -630,18 +833,34 @@ cudaError_t launch_op(const SortedPlan& plan, const T* value, int64_t n, int64_t
           plan.keys, plan.perm, ni, reinterpret_cast<const uint32_t*>(ws + L.off_seg_start),
           reinterpret_cast<const PlanHeader*>(ws + L.off_plan), value, P);
     } else {
-      // one wave of lane groups at 2 CTAs per SM.  The chunk size fixes the summation tree, so it must
-      // depend on (N, D) alone — not on the consumer or its register count (MergeAdd fits 3 CTAs per SM;
-      // the fast-mode optimizers must still reduce in exactly MergeAdd's order).
-      int chunk = choose_chunk(n, GPC * 2);
-      if (const char* ov = std::getenv("B200EMB_CHUNK")) {  // tuning override
-        const int c = std::atoi(ov);
-        if (c >= kMinChunk && c <= kMaxChunk) chunk = c;
-      }
+      // one wave of lane groups at 3 CTAs per SM.  The chunk size fixes the summation tree, so it must
+      // depend on (N, D) alone — not on the consumer (the fast-mode optimizers must reduce in exactly
+      // MergeAdd's order); how many CTAs of a given consumer really fit an SM only changes the timing.
+      static const int chunk_override = [] {
+        const char* ov = std::getenv("B200EMB_CHUNK");   // tuning override, read once
+        const int c = ov ? std::atoi(ov) : 0;
+        return (c >= kMinChunk && c <= kMaxChunk) ? c : 0;
+      }();
+      const int chunk = chunk_override ? chunk_override : choose_chunk(n, GPC * 3);
       const int ctas = static_cast<int>(ceil_div(n, static_cast<int64_t>(GPC) * chunk));
-      const size_t smem = sizeof(T) * 2 * GPC * COLS + sizeof(uint32_t) * 2 * GPC * chunk;
-      k_chunk_reduce<T, OP, LPR, NV, VEC><<<ctas, kBlock, smem, s>>>(plan.keys, plan.perm, ni, chunk,
-                                                                     value, P, C);
+      const int slack = std::min(kBoundarySlack, GPC * chunk / 2);
+      const size_t smem = Ring<T, OP, NV, VEC>::kBytes + sizeof(T) * 2 * GPC * COLS +
+                          sizeof(uint32_t) * 2 * (GPC * chunk + slack + 2);
+      const ChunkGeom G{ni, chunk, slack};
+      auto kern = k_chunk_reduce<T, OP, LPR, NV, VEC>;
+      // opt in to > 48 KB of dynamic shared memory once per device (the attribute is per device)
+      static std::atomic<unsigned long long> attr_done{0};
+      int dev = 0;
+      cudaGetDevice(&dev);
+      const unsigned long long bit = 1ull << (dev & 63);
+      if (!(attr_done.load(std::memory_order_relaxed) & bit)) {
+        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess) {
+          err = cudaGetLastError();
+          return;
+        }
+        attr_done.fetch_or(bit, std::memory_order_relaxed);
+      }
+      kern<<<ctas, kBlock, smem, s>>>(plan.keys, plan.perm, G, value, P, C);
     }
     err = cudaGetLastError();
   });
@@ -649,14 +868,6 @@ cudaError_t launch_op(const SortedPlan& plan, const T* value, int64_t n, int64_t
 }
 
 }  // namespace
-
-int choose_chunk(int64_t n, int groups_per_sm) {
-  // one full wave of lane groups across the chip's 148 SMs, chunk clamped to [4, 64]
-  const int64_t target_groups = 148LL * groups_per_sm;
-  int64_t c = ceil_div(n, target_groups);
-  c = std::max<int64_t>(kMinChunk, std::min<int64_t>(kMaxChunk, c));
-  return static_cast<int>(c);
-}
 
 template <typename T>
 cudaError_t launch_update(const SortedPlan& plan, const T* value, int64_t n, int64_t d,
@@ -676,12 +887,5 @@ cudaError_t launch_update(const SortedPlan& plan, const T* value, int64_t n, int
   }
   return cudaErrorInvalidValue;
 }
-
-template cudaError_t launch_update<float>(const SortedPlan&, const float*, int64_t, int64_t, int64_t,
-                                          const UpdateArgs<float>&, bool, char*, const Workspace&,
-                                          int32_t*, cudaStream_t);
-template cudaError_t launch_update<double>(const SortedPlan&, const double*, int64_t, int64_t,
-                                           int64_t, const UpdateArgs<double>&, bool, char*,
-                                           const Workspace&, int32_t*, cudaStream_t);
 
 }  // namespace b200emb

@@ -73,7 +73,8 @@ k_segment_scatter_i64(const int64_t* __restrict__ src, const int64_t* __restrict
 template <typename T, int LPR, int NV, bool VEC, int MODE>
 __global__ void __launch_bounds__(kBlock, 4)
 k_permute_rows(const T* __restrict__ src, const uint32_t* __restrict__ perm,
-               const uint32_t* __restrict__ uidx, int n, int d, T* __restrict__ out) {
+               const uint32_t* __restrict__ uidx, int n, int d, T* __restrict__ out, WaitSpec wait) {
+  wait_for_flags(wait.flags, wait.epoch, wait.world, wait.status);   // rows stored by other GPUs (sharded lookup)
   constexpr int EPV = Epv<T, VEC>::value;
   constexpr int kGroups = kBlock / LPR;
   constexpr int kRows = 4;
@@ -105,7 +106,14 @@ k_permute_rows(const T* __restrict__ src, const uint32_t* __restrict__ perm,
 #pragma unroll
         for (int k = 0; k < NV; ++k) {
           const int col = col0 + (l + k * LPR) * EPV;
-          if (live[r] && col < d) load_vec<T, VEC>(src + from[r] * d + col, v[r][k]);
+          if (live[r] && col < d) {
+            if (from[r] != static_cast<int64_t>(kNoKey)) {
+              load_vec<T, VEC>(src + from[r] * d + col, v[r][k]);
+            } else {   // an out-of-range id of the batch (no unique row): zeros, as the header promises
+#pragma unroll
+              for (int e = 0; e < EPV; ++e) v[r][k][e] = T(0);
+            }
+          }
         }
 #pragma unroll
       for (int r = 0; r < kRows; ++r)
@@ -158,7 +166,7 @@ cudaError_t launch_segment_scatter_i64(const int64_t* src, int64_t n_upper, cons
 
 template <typename T>
 cudaError_t launch_permute_rows(const T* src, const SortedPlan& plan, const uint32_t* uidx, int64_t n,
-                                int64_t d, T* out, int mode, cudaStream_t s) {
+                                int64_t d, T* out, int mode, cudaStream_t s, const WaitSpec& wait) {
   if (n == 0) return cudaSuccess;
   const bool aligned = is_aligned16(src) && is_aligned16(out);
   cudaError_t err = cudaSuccess;
@@ -167,21 +175,21 @@ cudaError_t launch_permute_rows(const T* src, const SortedPlan& plan, const uint
     const int grid = static_cast<int>(std::min<int64_t>(ceil_div(n, kGroups), 148 * 4));
     if (mode == 1)
       k_permute_rows<T, LPR, NV, VEC, 1><<<grid, kBlock, 0, s>>>(src, plan.perm, uidx, static_cast<int>(n),
-                                                                 static_cast<int>(d), out);
+                                                                 static_cast<int>(d), out, wait);
     else if (mode == 2)
       k_permute_rows<T, LPR, NV, VEC, 2><<<grid, kBlock, 0, s>>>(src, plan.perm, uidx, static_cast<int>(n),
-                                                                 static_cast<int>(d), out);
+                                                                 static_cast<int>(d), out, wait);
     else
       k_permute_rows<T, LPR, NV, VEC, 0><<<grid, kBlock, 0, s>>>(src, plan.perm, uidx, static_cast<int>(n),
-                                                                 static_cast<int>(d), out);
+                                                                 static_cast<int>(d), out, wait);
     err = cudaGetLastError();
   });
   return err;
 }
 
 template cudaError_t launch_permute_rows<float>(const float*, const SortedPlan&, const uint32_t*, int64_t,
-                                                int64_t, float*, int, cudaStream_t);
+                                                int64_t, float*, int, cudaStream_t, const WaitSpec&);
 template cudaError_t launch_permute_rows<double>(const double*, const SortedPlan&, const uint32_t*, int64_t,
-                                                 int64_t, double*, int, cudaStream_t);
+                                                 int64_t, double*, int, cudaStream_t, const WaitSpec&);
 
 }  // namespace b200emb

@@ -372,7 +372,9 @@ k_head_write(const uint32_t* __restrict__ skey, int n, uint32_t invalid_key,
   for (int j = 0; j < kItems; ++j) {
     const bool head = (headmask >> j) & 1u;
     run += head;
-    u[j] = run - 1u;  // (wraps for leading invalid-only data; never used)
+    // out-of-range ids (key == invalid_key) belong to no unique row: kNoKey tells expand_unique / the
+    // inverse map to hand back a zero row instead of some other id's embedding
+    u[j] = k[j] == invalid_key ? kNoKey : run - 1u;
     if (head && idx0 + j < n) {
       seg_start[u[j]] = static_cast<uint32_t>(idx0 + j);
       if (out_rows) out_rows[u[j]] = static_cast<int64_t>(k[j]);

@@ -63,8 +63,26 @@ def test_plan_unique_rows_matches_split_ids_semantics(capi, n, v, shards):
     valid = ids < v
     want = uvals.cpu().numpy()[np.minimum(plan.uidx, max(u, 1) - 1)][np.argsort(plan.perm, kind="stable")]
     assert np.array_equal(got[valid], want[valid])
+    assert not got[~valid].any()          # out-of-range ids come back as zero rows, never another id's row
     val = torch.from_numpy(rng.standard_normal((n, 8)).astype(np.float32)).cuda()
     assert np.array_equal(capi.gather_sorted(val, ph, ws).cpu().numpy(), val.cpu().numpy()[plan.perm])
+
+
+@pytest.mark.parametrize("shards", [1, 4])
+def test_expand_unique_all_ids_out_of_range(capi, shards):
+    """A batch with no valid id at all: U = 0, every expanded row is zero (nothing is read at a wrapped index)."""
+    n, v = 3000, 500
+    ids = torch.full((n,), v + 7, dtype=torch.int64, device="cuda")
+    ids[::3] = -1
+    ws = capi.alloc_workspace(n, 8)
+    status = capi.new_status()
+    ukeys, nu, bounds, eb, local = capi.plan_unique_rows(ids, v, shards, ws, status=status, want_elem_bounds=True)
+    assert int(nu.item()) == 0 and int(status.item()) & 2
+    assert bounds.cpu().tolist() == [0] * (shards + 1) and eb.cpu().tolist() == [0] * (shards + 1)
+    uvals = torch.full((4, 8), 3.5, device="cuda")
+    got = capi.expand_unique(uvals, n, capi.plan_height(v, shards), ws)
+    torch.cuda.synchronize()
+    assert not got.cpu().numpy().any()
 
 
 @pytest.mark.parametrize("deterministic", [True, False], ids=["bit-exact", "fast"])
