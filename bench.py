@@ -174,10 +174,190 @@ def workload_name(gpus):
 
 
 # --------------------------------------------------------------------------- single GPU
+def _ref_module():
+    """The CPU checker: oracle/_ref (the reference's own kernels) when built, else the oracle restatement."""
+    import oracle
+    try:
+        from oracle import ref_cpu
+        if ref_cpu.available():
+            return ref_cpu, "reference"
+    except Exception:
+        pass
+    return oracle, "port"
+
+
+def parity_c2(torch, capi, synth, dev):
+    """The north_star bars on configs[1] at full size, against the reference CPU kernels on the same inputs:
+    gathered rows bit-exact; bit-exact mode bit-exact; fast mode — the literal metric (fraction and max of
+    |fast - ref_fp32| / |ref_fp32| > 1e-6 over the updated table) beside the reordering bound vs fp64."""
+    import oracle
+    ref, kind = _ref_module()
+    v, d, n, a, _ = synth.CONFIGS["C2_ctr_sgd"]
+    table0 = synth.table_values(v, d)
+    ids = synth.ZipfIds(v, a, seed=7).sample(n)
+    grad = synth.grad_values(n, d, seed=77)
+    lr = np.array([0.01], np.float32)
+    want = table0.copy()
+    want_out = ref.lookup_table(want, ids)
+    ref.sgd_sparse(want, ids, grad, lr)
+    d_ids, d_grad, d_lr = torch.from_numpy(ids).to(dev), torch.from_numpy(grad).to(dev), torch.from_numpy(lr).to(dev)
+    res = {"checker": "oracle/_ref (reference CPU kernels, unmodified sources)" if kind == "reference" else "oracle (CPU restatement)",
+           "config": "configs[1] full size, one step, seed 7"}
+    t = torch.from_numpy(table0).to(dev)
+    out = capi.lookup_table(t, d_ids)
+    res["gather_bit_exact"] = bool(np.array_equal(out.cpu().numpy().view(np.uint32), want_out.view(np.uint32)))
+    capi.sparse_sgd(t, d_ids, d_grad, d_lr, flags=capi.DETERMINISTIC)
+    res["det_bit_exact"] = bool(np.array_equal(t.cpu().numpy().view(np.uint32), want.view(np.uint32)))
+    t = torch.from_numpy(table0).to(dev)
+    capi.sparse_sgd(t, d_ids, d_grad, d_lr)
+    fast = t.cpu().numpy()
+    touched = np.unique(ids)
+    rel = np.abs(fast[touched].astype(np.float64) - want[touched]) / np.maximum(np.abs(want[touched]), 1e-30)
+    res["fast_frac_gt_1e-6_rel_vs_ref"] = float((rel > 1e-6).mean())
+    res["fast_max_rel_vs_ref"] = float(rel.max())
+    rows, merged = oracle.merge_add(ids, grad, truth=True)
+    _, l1 = oracle.merge_add(ids, np.abs(grad), truth=True)
+    truth = table0[rows].astype(np.float64) - 0.01 * merged
+    bound = 1e-6 * (np.abs(table0[rows]) + 0.01 * l1)
+    res["fast_within_reordering_bound_vs_fp64"] = bool((np.abs(fast[rows] - truth) <= bound + 1e-30).all())
+    err_fast = np.abs(fast[rows] - truth).max()
+    err_ref = np.abs(want[rows] - truth).max()
+    res["max_abs_err_vs_fp64"] = {"fast": float(err_fast), "reference_order_fp32": float(err_ref)}
+    res["untouched_rows_unchanged"] = bool(np.array_equal(np.delete(fast, touched, axis=0)[:50000], np.delete(table0, touched, axis=0)[:50000]))
+    res["ok"] = bool(res["gather_bit_exact"] and res["det_bit_exact"] and res["fast_within_reordering_bound_vs_fp64"]
+                     and res["untouched_rows_unchanged"])
+    return res
+
+
+def extra_config(torch, capi, synth, stepbench, name, dev, peak, steps):
+    """One of the larger single-GPU configs (configs[2] lazy Adam, configs[4] duplicate-heavy SGD): device-timed
+    step through the same pipeline, per-phase times, roofline fractions, and a shortened parity check (sampled
+    rows incl. the hottest id, bit-exact mode vs the oracle, fast mode within the reordering bound)."""
+    import oracle
+    v, d, n, a, opt = synth.CONFIGS[name]
+    per_buf = n * (8 + 2 * 4 * d)
+    nb = max(2, min(8, int(np.ceil(300e6 / per_buf))))
+    z = synth.ZipfIds(v, a, seed=0)
+    ids_np = [z.sample(n) for _ in range(nb)]
+    del z
+    u_mean = float(np.mean([len(np.unique(i)) for i in ids_np]))
+    g = torch.Generator(device=dev)
+    g.manual_seed(1234)
+    table = torch.empty((v, d), dtype=torch.float32, device=dev)
+    for lo in range(0, v, 1 << 22):
+        table[lo:lo + (1 << 22)].uniform_(-0.05, 0.05, generator=g)
+    ids = [torch.from_numpy(i).to(dev) for i in ids_np]
+    dout = [torch.randn((n, d), device=dev, generator=g) * 0.01 for _ in range(nb)]
+    lr_v = 0.001 if opt == "adam" else 0.01
+    # ---- parity first (one step on batch 0, sampled rows), on the pristine table
+    uniq, counts = np.unique(ids_np[0], return_counts=True)
+    rng = np.random.default_rng(5)
+    rows_np = np.unique(np.concatenate([[uniq[np.argmax(counts)]], rng.choice(uniq, size=min(256, uniq.size), replace=False)]))
+    rows_d = torch.from_numpy(rows_np).to(dev)
+    pos = torch.nonzero(torch.isin(ids[0], rows_d)).reshape(-1)
+    sub_ids = torch.searchsorted(rows_d, ids[0][pos]).cpu().numpy()
+    sub_grad = dout[0][pos].cpu().numpy()
+    before = table[rows_d].cpu().numpy()
+    lr_t = torch.tensor([lr_v], device=dev)
+    parity = {"sampled_rows": int(rows_np.size), "max_duplicates_of_one_id": int(counts.max())}
+    ws = capi.alloc_workspace(n, d, 4, dev)
+    if opt == "adam":
+        b1p, b2p = torch.tensor([0.9], device=dev), torch.tensor([0.999], device=dev)
+        want = [before.copy(), np.zeros_like(before), np.zeros_like(before)]
+        oracle.adam_sparse(want[0], want[1], want[2], sub_ids, sub_grad, np.array([lr_v], np.float32),
+                           np.array([0.9], np.float32), np.array([0.999], np.float32))
+        m1, m2 = torch.zeros_like(table), torch.zeros_like(table)
+        capi.sparse_adam(table, m1, m2, ids[0], dout[0], lr_t, b1p, b2p, workspace=ws, flags=capi.DETERMINISTIC)
+        got = [t[rows_d].cpu().numpy() for t in (table, m1, m2)]
+        parity["det_bit_exact"] = bool(all(np.array_equal(x.view(np.uint32), w.view(np.uint32)) for x, w in zip(got, want)))
+        table[rows_d] = torch.from_numpy(before).to(dev)      # undo on the sampled rows, then the fast mode on them
+        m1.zero_(); m2.zero_()
+        # (rows outside the sample were stepped once in bit-exact mode: irrelevant for the timing that follows)
+        capi.sparse_adam(table, m1, m2, ids[0], dout[0], lr_t, b1p, b2p, workspace=ws)
+        fm1 = m1[rows_d].cpu().numpy()
+        _, l1 = oracle.merge_add(sub_ids, np.abs(sub_grad), truth=True)
+        parity["fast_within_bound"] = bool((np.abs(fm1.astype(np.float64) - want[1]) <= 1e-6 * (np.abs(want[1]) + 0.1 * l1) + 1e-12).all())
+        del m1, m2
+    else:
+        want = before.copy()
+        oracle.sgd_sparse(want, sub_ids, sub_grad, np.array([lr_v], np.float32))
+        capi.sparse_sgd(table, ids[0], dout[0], lr_t, workspace=ws, flags=capi.DETERMINISTIC)
+        parity["det_bit_exact"] = bool(np.array_equal(table[rows_d].cpu().numpy().view(np.uint32), want.view(np.uint32)))
+        table[rows_d] = torch.from_numpy(before).to(dev)
+        capi.sparse_sgd(table, ids[0], dout[0], lr_t, workspace=ws)
+        _, l1 = oracle.merge_add(sub_ids, np.abs(sub_grad), truth=True)
+        _, msum = oracle.merge_add(sub_ids, sub_grad, truth=True)
+        truth = before.astype(np.float64) - lr_v * msum
+        parity["fast_within_bound"] = bool((np.abs(table[rows_d].cpu().numpy() - truth) <= 1e-6 * (np.abs(before) + lr_v * l1)).all())
+    out0 = capi.lookup_table(table, ids[0][:65536])
+    parity["gather_bit_exact"] = bool(torch.equal(out0, table[ids[0][:65536]]))
+    parity["ok"] = bool(parity["det_bit_exact"] and parity["fast_within_bound"] and parity["gather_bit_exact"])
+    del ws, out0
+    # ---- timing
+    pipe = stepbench.SingleGpuPipeline(table, ids, dout, opt, lr_v)
+    pipe.capture()
+    ms = pipe.time_steps(steps, max(3, nb))
+    ph = pipe.phase_times(max(6, steps // 2))
+    by = synth.algorithmic_bytes(n, d, u_mean, opt)
+    t_step = ms / steps * 1e-3
+    res = {"config": name, "table": [v, d], "ids_per_step": n, "unique_ids_per_step": u_mean, "optimizer": opt,
+           "ms_per_step": ms / steps, "value": n / t_step, "unit": UNIT, "steps": steps, "batch_buffers": nb,
+           "phases": {"gather_us": ph["gather"] * 1e6, "sort_plan_us": ph["sort_plan"] * 1e6,
+                      "reduce_update_us": ph["update"] * 1e6, "serial_step_us": ph["serial"] * 1e6},
+           "roofline": {"bound": "hbm", "unit": "GB/s", "peak": peak,
+                        "step": {"algorithmic_bytes": by["step"], "achieved": by["step"] / t_step / 1e9,
+                                 "frac": by["step"] / t_step / 1e9 / peak},
+                        "gather": {"algorithmic_bytes": by["fwd"], "frac": by["fwd"] / ph["gather"] / 1e9 / peak},
+                        "reduce_update": {"algorithmic_bytes": by["upd"], "frac": by["upd"] / ph["update"] / 1e9 / peak}},
+           "parity": parity, "status_word": int(pipe.status.item())}
+    del pipe, table, ids, dout
+    torch.cuda.empty_cache()
+    return res
+
+
+def e2e_opkernel(torch, pkg, table_np, ids_h, dout_h, n, d, v, steps):
+    """The same step through the drop-in boundary a Fluid program reaches: Operator.run of the registered
+    lookup_table -> lookup_table_grad (is_sparse) -> sgd CUDA OpKernels (paddle-1_b200/fluid/, REGISTER_OP_CUDA_KERNEL)
+    on host numpy batches: feed (H2D) ids and Out@GRAD, run the three ops, fetch Out (D2H), synchronously like
+    Executor::Run does (framework/executor.cc:332-340)."""
+    from importlib import import_module
+    core = import_module("paddle1_b200.fluid_lite")
+    place = core.CUDAPlace(0)
+    scope = core.Scope()
+    scope.var("W").get_tensor().set(table_np, place)
+    scope.var("LearningRate").get_tensor().set(np.array([0.01], np.float32), place)
+    lookup = core.Operator("lookup_table", W="W", Ids="Ids", Out="Out", is_sparse=True)
+    grad = core.Operator("lookup_table_grad", W="W", Ids="Ids", **{"Out@GRAD": "Out@GRAD", "W@GRAD": "W@GRAD"}, is_sparse=True)
+    sgd = core.Operator("sgd", Param="W", Grad="W@GRAD", LearningRate="LearningRate", ParamOut="W")
+    ids_np = [t.numpy().reshape(-1, 1) for t in ids_h]
+    dout_np = [t.numpy() for t in dout_h]
+
+    def one(i):
+        b = i % len(ids_np)
+        scope.var("Ids").get_tensor().set(ids_np[b], place)
+        scope.var("Out@GRAD").get_tensor().set(dout_np[b], place)
+        lookup.run(scope, place)
+        grad.run(scope, place)
+        sgd.run(scope, place)
+        return np.array(scope.find_var("Out").get_tensor())
+    for i in range(3):
+        one(i)
+    t0 = time.perf_counter()
+    for i in range(steps):
+        one(i)
+    el = time.perf_counter() - t0
+    return {"value": n * steps / el, "unit": UNIT, "ms_per_step": el / steps * 1e3, "steps": steps,
+            "h2d_bytes_per_step": n * 8 + n * d * 4, "d2h_bytes_per_step": n * d * 4,
+            "api": "fluid_lite.Operator('lookup_table' | 'lookup_table_grad' | 'sgd').run(scope, CUDAPlace(0)) — the "
+                   "registered OpKernel wrappers; pageable numpy feeds, synchronous feed/run/fetch"}
+
+
 def run_single(args):
     import torch
+    from importlib import import_module
     pkg = load_pkg()
     capi, synth = pkg.capi, pkg.synth
+    stepbench = import_module("paddle1_b200.stepbench")
     capi.lib()  # raises if the CUDA library is missing: no fallback
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (use --impl reference for the CPU arm)")
@@ -186,8 +366,8 @@ def run_single(args):
     v, d, n, a, opt = synth.CONFIGS["C2_ctr_sgd"]
     peak, peak_src = measured_peak_gbs()
 
-    table = torch.from_numpy(synth.table_values(v, d)).to(dev)
-    lr = torch.tensor([0.01], dtype=torch.float32, device=dev)
+    table_np = synth.table_values(v, d)
+    table = torch.from_numpy(table_np).to(dev)
     z = synth.ZipfIds(v, a, seed=0)
     ids_h, dout_h, uniq = [], [], []
     for b in range(N_ROTATE):
@@ -198,165 +378,91 @@ def run_single(args):
     u_mean = float(np.mean(uniq))
     ids = [t.to(dev) for t in ids_h]
     dout = [t.to(dev) for t in dout_h]
-    out = [torch.empty((n, d), dtype=torch.float32, device=dev) for _ in range(N_ROTATE)]
-    ws = [capi.alloc_workspace(n, d, 4, dev) for _ in range(N_ROTATE)]
-    status = capi.new_status(dev)
     bytes_ = synth.algorithmic_bytes(n, d, u_mean, opt)
 
-    # the critical path (gather -> reduce/update) gets the high-priority stream; the sort plans of the
-    # following batches fill in behind it on normal-priority streams
-    main = torch.cuda.Stream(dev, priority=-1)
-    side = torch.cuda.Stream(dev, priority=0)
-
-    def step(b):
-        """One step on batch b.  The sort plan of the NEXT batch (ids only, like a data-loader prefetch)
-        runs on the side stream while this batch's gather + fused reduce/update run on the main one;
-        every step still launches exactly one plan, one gather, one update."""
-        nb = (b + 1) % N_ROTATE
-        side.wait_stream(main)
-        with torch.cuda.stream(side):
-            capi.plan_rows(ids[nb], v, ws[nb], status)
-        capi.lookup_table(table, ids[b], -1, out[b], status)
-        # lookup_table_grad (sparse): the SelectedRows gradient aliases ids / dOut — zero copy
-        capi.sparse_sgd(table, ids[b], dout[b], lr, ws[b], capi.PLAN_READY, status)
-        main.wait_stream(side)
-
-    # gather, sort plan, chunk reduce (fast-mode SGD finds the run heads itself: no head scan)
-    kernels_per_step = 1 + capi.plan_kernel_count(n, v) + 1
-
-    graphs = []
-    with torch.cuda.stream(main):
-        for b in range(N_ROTATE):   # every workspace holds its batch's plan before the first step
-            capi.plan_rows(ids[b], v, ws[b], status)
-        for b in range(N_ROTATE):   # warm every path once outside capture
-            step(b)
-        main.synchronize()
-        for b in range(N_ROTATE):
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g, stream=main):
-                step(b)
-            graphs.append(g)
-        # one graph holding a whole rotation (N_ROTATE consecutive steps): amortises the per-graph launch gap
-        rotation = torch.cuda.CUDAGraph()
-        side2 = torch.cuda.Stream(dev, priority=0)
-        with torch.cuda.graph(rotation, stream=main):
-            # Inside a rotation the plan of batch b+1 only has to be ready when update(b+1) starts, so the
-            # plans run as two alternating side chains that overlap gather AND update of the main stream.
-            sides = [side, side2]
-            for st in sides:
-                st.wait_stream(main)
-            plan_done, upd0_done = {}, None
-            for b in range(N_ROTATE):
-                nb = (b + 1) % N_ROTATE
-                st = sides[nb % 2]
-                with torch.cuda.stream(st):
-                    if nb == 0:
-                        st.wait_event(upd0_done)          # ws[0] is still read by this rotation's update(0)
-                    capi.plan_rows(ids[nb], v, ws[nb], status)
-                    plan_done[nb] = torch.cuda.Event()
-                    plan_done[nb].record(st)
-                capi.lookup_table(table, ids[b], -1, out[b], status)
-                if b in plan_done:
-                    main.wait_event(plan_done[b])
-                capi.sparse_sgd(table, ids[b], dout[b], lr, ws[b], capi.PLAN_READY, status)
-                if b == 0:
-                    upd0_done = torch.cuda.Event()
-                    upd0_done.record(main)
-            for st in sides:
-                main.wait_stream(st)
-    torch.cuda.synchronize()
-
-    def run_steps(k, start=0):
-        """k consecutive steps starting at batch `start % N_ROTATE`: whole rotations as one graph launch,
-        the ragged head/tail as single-step graphs."""
-        i = 0
-        while i < k and (start + i) % N_ROTATE != 0:
-            graphs[(start + i) % N_ROTATE].replay()
-            i += 1
-        while k - i >= N_ROTATE:
-            rotation.replay()
-            i += N_ROTATE
-        while i < k:
-            graphs[(start + i) % N_ROTATE].replay()
-            i += 1
-
-    with torch.cuda.stream(main):
-        run_steps(args.warmup)
+    pipe = stepbench.SingleGpuPipeline(table, ids, dout, opt, 0.01)
+    status, lr = pipe.status, pipe.lr
+    pipe.capture()
+    kernels_per_step = pipe.kernels_per_step()
+    with torch.cuda.stream(pipe.main):
+        pipe.run_steps(args.warmup)
         torch.cuda.synchronize()
         sampler = ClockSampler(0)
         sampler.start()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(main)
-        run_steps(args.steps, args.warmup)
-        e1.record(main)
+        e0.record(pipe.main)
+        pipe.run_steps(args.steps, args.warmup)
+        e1.record(pipe.main)
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1)
         # keep the GPU under the same load a little longer so the clock sampler sees it
         t_end = time.perf_counter() + 0.25
         while time.perf_counter() < t_end:
-            run_steps(50)
+            pipe.run_steps(50)
             torch.cuda.synchronize()
         clocks = sampler.stop()
     ms_per_step = ms / args.steps
     value = n * args.steps / (ms * 1e-3)
 
     # ---- per-phase timings (CUDA events on the launching stream, same rotating buffers) ----------
-    def time_phase(fn, reps):
-        with torch.cuda.stream(main):
-            for b in range(N_ROTATE):
-                fn(b)
-            main.synchronize()
-            gs = []
-            for b in range(N_ROTATE):
-                g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g, stream=main):
-                    fn(b)
-                gs.append(g)
-            for i in range(N_ROTATE):
-                gs[i].replay()
-            main.synchronize()
-            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a0.record(main)
-            for i in range(reps):
-                gs[i % N_ROTATE].replay()
-            a1.record(main)
-            main.synchronize()
-            return a0.elapsed_time(a1) / reps * 1e-3
-
     reps = max(50, min(args.steps, 400))
-    t_gather = time_phase(lambda b: capi.lookup_table(table, ids[b], -1, out[b], status), reps)
-    t_plan = time_phase(lambda b: capi.plan_rows(ids[b], v, ws[b], status), reps)
-    for b in range(N_ROTATE):
-        capi.plan_rows(ids[b], v, ws[b], status)
-    t_update = time_phase(lambda b: capi.sparse_sgd(table, ids[b], dout[b], lr, ws[b], capi.PLAN_READY, status), reps)
+    ph = pipe.phase_times(reps)
+    t_gather, t_plan, t_update = ph["gather"], ph["sort_plan"], ph["update"]
+    t_det = pipe.time_phase(lambda b: (pipe.gather(b), pipe.update(b, capi.DETERMINISTIC)), max(5, reps // 20))
     phases = {
         "gather_us": t_gather * 1e6, "sort_plan_us": t_plan * 1e6, "reduce_update_us": t_update * 1e6,
+        "serial_step_us": ph["serial"] * 1e6,
         "gather_GBs": bytes_["fwd"] / t_gather / 1e9, "reduce_update_GBs": bytes_["upd"] / t_update / 1e9,
+        "note": "each phase replayed alone as CUDA graphs over the rotating buffers; sort_plan moves 8 B per id per "
+                "radix pass (not in the algorithmic bytes: SURVEY 8d counts it as overhead); serial_step = gather + "
+                "sort + update back to back on one stream (what one OpKernel call sequence costs without the prefetch)",
     }
-    if t_gather >= t_update:
-        dom = {"kernel": "k_gather (lookup_table fwd)", "bytes": bytes_["fwd"], "t": t_gather}
-    else:
-        dom = {"kernel": "k_chunk_reduce (fused MergeAdd+SGD)", "bytes": bytes_["upd"], "t": t_update}
-    achieved = dom["bytes"] / dom["t"] / 1e9
+    cand = [("k_gather (lookup_table fwd)", bytes_["fwd"], t_gather),
+            ("k_chunk_reduce (fused MergeAdd+SGD)", bytes_["upd"], t_update),
+            ("sort plan (k_prepare_direct + k_radix_pass_direct x passes)", 0, t_plan)]
+    hbm = [c for c in cand if c[1] > 0]
+    dom = max(hbm, key=lambda c: c[2])
+    achieved = dom[1] / dom[2] / 1e9
     # DRAM traffic of the same kernel(s) from the committed `ncu --set full` capture (profiles/), per launch
     traffic = None
-    try:
-        with open(os.path.join(ROOT, "profiles", "r1_ncu_full_summary.json")) as f:
-            prof = json.load(f)
-        keys = ["k_gather"] if dom["kernel"].startswith("k_gather") else ["k_chunk_reduce"]
-        traffic = sum(v["dram_traffic_bytes_per_launch"] for k, v in prof.items() if any(k.startswith(q) for q in keys))
-    except Exception:
-        traffic = None
+    for fname in ("r2_ncu_full_summary.json", "r1_ncu_full_summary.json"):
+        try:
+            with open(os.path.join(ROOT, "profiles", fname)) as f:
+                prof = json.load(f)
+            keys = ["k_gather"] if dom[0].startswith("k_gather") else ["k_chunk_reduce"]
+            traffic = sum(v_["dram_traffic_bytes_per_launch"] for k, v_ in prof.items() if any(k.startswith(q) for q in keys))
+            break
+        except Exception:
+            traffic = None
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "kernel": dom["kernel"], "algorithmic_bytes_per_launch": dom["bytes"],
+                "traffic": traffic, "kernel": dom[0], "algorithmic_bytes_per_launch": dom[1],
                 "peak_source": peak_src,
+                "longest_phase": max(cand, key=lambda c: c[2])[0],
+                "phases_frac": {"gather": bytes_["fwd"] / t_gather / 1e9 / peak,
+                                "reduce_update": bytes_["upd"] / t_update / 1e9 / peak,
+                                "serial_step (gather + sort plan + update, no overlap)": bytes_["step"] / ph["serial"] / 1e9 / peak},
                 "step": {"algorithmic_bytes": bytes_["step"], "achieved": bytes_["step"] / (ms_per_step * 1e-3) / 1e9,
                          "frac": bytes_["step"] / (ms_per_step * 1e-3) / 1e9 / peak}}
 
     # ---- end to end: host buffers, H2D of ids+dOut and D2H of Out inside the timed region ---------
     e2e = run_e2e(torch, capi, table, lr, ids_h, dout_h, n, d, v, status, max(20, min(args.steps, 200)))
+    try:
+        e2e_ok = e2e_opkernel(torch, pkg, table_np, ids_h, dout_h, n, d, v, max(10, min(args.steps, 50)))
+    except Exception as e:  # the wrappers are a separate library: report, do not hide
+        e2e_ok = {"error": str(e)[:300]}
 
     st = int(status.item())
+    parity = parity_c2(torch, capi, synth, dev)
+    del pipe, table, ids, dout
+    torch.cuda.empty_cache()
+    extra = []
+    if not getattr(args, "quick", False):
+        free, _ = torch.cuda.mem_get_info()
+        for name, need in (("C3_adam", 30e9), ("C5_dup_heavy", 100e9)):
+            if free < need:
+                extra.append({"config": name, "skipped": "needs %.0f GB of free device memory" % (need / 1e9)})
+                continue
+            extra.append(extra_config(torch, capi, synth, stepbench, name, dev, peak, 30 if name == "C3_adam" else 8))
     cpu = time_cpu(synth.CONFIGS["C2_ctr_sgd"], budget_s=10.0)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
@@ -367,10 +473,14 @@ def run_single(args):
                    "l2": "inputs rotate over %d batch buffers (%.0f MB ids+dOut+Out) > 126 MB L2; table 256 MB"
                          % (N_ROTATE, N_ROTATE * (n * 8 + 2 * n * d * 4) / 1e6),
                    "launch": "CUDA graphs (one per rotation of %d steps, single-step graphs for the remainder);" % N_ROTATE + " the sort plan of batch i+1 runs on a side stream during step i (ids-only prefetch), gather+update of batch i on the main stream"},
-        "roofline": roofline, "phases": phases, "cpu_baseline": {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")},
-        "e2e": e2e, "gpu_launches": kernels_per_step * args.steps, "clocks": clocks, "status_word": st,
+        "roofline": roofline, "phases": phases, "det_ms_per_step": t_det * 1e3,
+        "cpu_baseline": {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": e2e, "e2e_opkernel": e2e_ok, "parity": parity, "configs_extra": extra,
+        "gpu_launches": kernels_per_step * args.steps, "clocks": clocks, "status_word": st,
     }
     print(json.dumps(line))
+    if not parity["ok"] or any(not x.get("parity", {}).get("ok", True) for x in extra):
+        raise SystemExit("parity check FAILED: %s" % json.dumps({"c2": parity, "extra": [x.get("parity") for x in extra]}))
 
 
 def run_e2e(torch, capi, table, lr, ids_h, dout_h, n, d, v, status, steps):
@@ -428,7 +538,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=40)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--ids-per-gpu", type=int, default=0, dest="ids_per_gpu",
-                    help="sharded runs: ids per GPU per step (default 16 x 4096 x 26)")
+                    help="sharded runs: ids per GPU per step (default 4096 x 26, the batch of configs[1])")
+    ap.add_argument("--quick", action="store_true", help="skip configs_extra (C3 / C5) and the sharded sweep")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":
@@ -436,10 +547,10 @@ def main():
         return
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.gpus > 1 or world > 1:
-        from importlib import import_module
-        sys.path.insert(0, ROOT)
-        load_pkg()
-        import_module("paddle1_b200.sharded_bench").run(args)
+        if args.quick:
+            os.environ["B200EMB_BENCH_QUICK"] = "1"
+        import bench_sharded
+        bench_sharded.run(args)
         return
     run_single(args)
 

@@ -270,7 +270,8 @@ int b200emb_exchange_maps(const int64_t* split_table, int world, int cols, int r
  * create   (allocates; current device = this rank's GPU).  `shard` = this rank's rows [ceil(height/world), d]
  *          (row i holds global row i*world + rank), moment1/moment2 alike for Adam (NULL for SGD).
  *          max_ids_per_step bounds n of prepare(); max_recv_rows bounds the unique rows all ranks together
- *          request from this owner in one step.  Exceeding either sets B200EMB_STATUS_SHARD_OVERFLOW in the
+ *          request from one owner in one step.  Both (and world, height, d) must be the SAME on every rank —
+ *          the ranks address each other's blocks by layout; connect() returns B200EMB_E_INVALID otherwise.  Exceeding either sets B200EMB_STATUS_SHARD_OVERFLOW in the
  *          status word and drops the excess rows.
  * export / connect   exchange of the per-rank blocks between processes: export() yields a 64-byte CUDA IPC
  *          handle; the caller all-gathers the handles with whatever transport it has (NCCL, MPI,
@@ -279,7 +280,8 @@ int b200emb_exchange_maps(const int64_t* split_table, int world, int cols, int r
  *          (b200emb_shard_block) to connect_ptrs() instead, with peer access enabled by the caller.
  * prepare  the ids-only part of a step — sort plan, de-duplication, split points per owner — into one of 4
  *          slots; needs nothing but the ids, so a training loop can run it for batch i+1 on another stream
- *          while batch i is in flight.  `ids` must stay valid until update() of that slot has run.
+ *          while batch i is in flight.  `ids` must stay valid until update() of that slot has run, and
+ *          prepare(slot) overwrites the slot: order it (stream wait) after the update() that last used it.
  * lookup   out[k,:] = table[ids[k],:] for the slot's ids (lookup_table_op.h:36-84 over the sharded table).
  * update   sparse SGD / lazy Adam of the sharded table with the SelectedRows gradient {rows = the slot's ids,
  *          value = d_out} (sgd_op.h:47-81, adam_op.h:158-220,282-321): merged locally, merged rows sent to

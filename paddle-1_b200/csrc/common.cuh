@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <cstdlib>
 
 namespace b200emb {
 
@@ -138,6 +139,31 @@ __device__ __forceinline__ void wait_for_flags(const unsigned long long* flags, 
   __syncthreads();
 }
 
+// Producer side (SignalSpec, internal.h); call with the whole CTA as the last thing a kernel does.
+__device__ __forceinline__ void signal_peers(unsigned long long* const* flag_dst, int64_t* const* payload_dst,
+                                             const int64_t* starts, const unsigned long long* epoch,
+                                             unsigned int* done_ctr, int world) {
+  if (flag_dst == nullptr) return;
+  __threadfence_system();            // this thread's stores to peer memory are performed system-wide
+  __syncthreads();
+  __shared__ bool s_last_cta;
+  if (threadIdx.x == 0) s_last_cta = atomicAdd(done_ctr, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!s_last_cta) return;
+  __threadfence_system();            // the other CTAs' fenced stores, observed through the counter
+  if (static_cast<int>(threadIdx.x) < world) {
+    const int r = threadIdx.x;
+    if (payload_dst) {
+      payload_dst[r][0] = starts[r];
+      payload_dst[r][1] = starts[r + 1] - starts[r];
+      __threadfence_system();
+    }
+    const unsigned long long e = *reinterpret_cast<const volatile unsigned long long*>(epoch);
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(flag_dst[r]), "l"(e) : "memory");
+  }
+  if (threadIdx.x == 0) *done_ctr = 0;
+}
+
 // ---------------------------------------------------------------------------
 // Row-shape dispatch: picks (LPR, NV, VEC) from D and pointer alignment and calls
 // f.template operator()<LPR, NV, VEC>().
@@ -159,5 +185,40 @@ inline void dispatch_row_shape(int64_t d, bool aligned16, F&& f) {
 }
 
 inline bool is_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// ---------------------------------------------------------------------------
+// Programmatic dependent launch (opt-in, B200EMB_PDL=1): a row kernel launched right behind another kernel of
+// the same stream may be set up (launch processing, CTA placement as SMs drain) while its predecessor is
+// still running; it blocks in pdl_wait() — the first thing it executes, before any global memory access —
+// until the predecessor has completed and its writes are visible.  Without the launch attribute both
+// instructions are no-ops.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+inline bool pdl_enabled() {
+  static const bool on = [] {
+    const char* v = std::getenv("B200EMB_PDL");
+    return v != nullptr && v[0] != '0';
+  }();
+  return on;
+}
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_row_kernel(void (*kernel)(KArgs...), int grid, int block, size_t smem, cudaStream_t s,
+                                     Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(static_cast<unsigned>(grid));
+  cfg.blockDim = dim3(static_cast<unsigned>(block));
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  if (pdl_enabled()) {
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+  }
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 
 }  // namespace b200emb

@@ -23,7 +23,9 @@ template <typename T, int LPR, int NV, bool VEC>
 __global__ void __launch_bounds__(kBlock, 4)
 k_gather(const T* __restrict__ table, const int64_t* __restrict__ ids, T* __restrict__ out,
          int64_t n, int64_t height, int d, int64_t padding_idx, int32_t* status,
-         const int64_t* __restrict__ seg_start, T* const* __restrict__ seg_dst, int segs) {
+         const int64_t* __restrict__ seg_start, T* const* __restrict__ seg_dst, int segs, SignalSpec sig) {
+  pdl_wait();
+  pdl_launch_dependents();
   if (segs > 0) n = min(n, seg_start[segs]);   // sharded owner side: the live count exists on the device only
   constexpr int EPV = Epv<T, VEC>::value;
   constexpr int kGroups = kBlock / LPR;
@@ -89,6 +91,7 @@ k_gather(const T* __restrict__ table, const int64_t* __restrict__ ids, T* __rest
     }
   }
   if (bad && status) atomicOr(status, 1);
+  signal_peers(sig.flag_dst, sig.payload_dst, sig.starts, sig.epoch, sig.done_ctr, sig.world);
 }
 
 
@@ -174,8 +177,8 @@ k_gather_bulk(const T* __restrict__ table, const int64_t* __restrict__ ids, T* _
 template <typename T>
 cudaError_t launch_gather(const T* table, int64_t height, int64_t d, const int64_t* ids, int64_t n,
                           int64_t padding_idx, T* out, int32_t* status, cudaStream_t s,
-                          const int64_t* seg_start, T* const* seg_dst, int segs) {
-  if (n == 0) return cudaSuccess;
+                          const int64_t* seg_start, T* const* seg_dst, int segs, const SignalSpec& signal) {
+  if (n == 0 && signal.flag_dst == nullptr) return cudaSuccess;
   const bool aligned = is_aligned16(table) && (segs > 0 || is_aligned16(out));
   // wide rows (>= 512 B): TMA bulk row copies — opt-in (B200EMB_GATHER_BULK=1).  Measured on B200 the
   // un-pipelined bulk path loses to the 128-bit LDG/STG path, which already runs near the HBM roofline for
@@ -199,21 +202,24 @@ cudaError_t launch_gather(const T* table, int64_t height, int64_t d, const int64
   dispatch_row_shape<T>(d, aligned, [&]<int LPR, int NV, bool VEC>() {
     constexpr int kGroups = kBlock / LPR;
     // one resident wave (4 CTAs of 256 threads per SM leaves room for the concurrent sort cluster)
+    static const int cps = [] {   // resident CTAs per SM the grid aims at (tuning override, read once)
+      const char* ov = std::getenv("B200EMB_GATHER_CPS");
+      const int c = ov ? std::atoi(ov) : 0;
+      return (c >= 1 && c <= 8) ? c : 4;
+    }();
     const int64_t want = ceil_div(n, static_cast<int64_t>(kGroups));
-    const int grid = static_cast<int>(std::min<int64_t>(want, 148 * 4));
-    k_gather<T, LPR, NV, VEC><<<grid, kBlock, 0, s>>>(table, ids, out, n, height,
-                                                      static_cast<int>(d), padding_idx, status,
-                                                      seg_start, seg_dst, segs);
-    err = cudaGetLastError();
+    const int grid = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(want, 148 * cps)));
+    err = launch_row_kernel(k_gather<T, LPR, NV, VEC>, grid, kBlock, 0, s, table, ids, out, n, height,
+                            static_cast<int>(d), padding_idx, status, seg_start, seg_dst, segs, signal);
   });
   return err;
 }
 
 template cudaError_t launch_gather<float>(const float*, int64_t, int64_t, const int64_t*, int64_t,
                                           int64_t, float*, int32_t*, cudaStream_t, const int64_t*,
-                                          float* const*, int);
+                                          float* const*, int, const SignalSpec&);
 template cudaError_t launch_gather<double>(const double*, int64_t, int64_t, const int64_t*, int64_t,
                                            int64_t, double*, int32_t*, cudaStream_t, const int64_t*,
-                                           double* const*, int);
+                                           double* const*, int, const SignalSpec&);
 
 }  // namespace b200emb

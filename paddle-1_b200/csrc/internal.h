@@ -108,13 +108,28 @@ struct WaitSpec {
   int32_t* status = nullptr;                   // B200EMB_STATUS_BARRIER_TIMEOUT after ~20 s
 };
 
+// Optional publication at the end of a producer kernel of the sharded path.  Every thread fences its stores to
+// the other GPUs (fence.sys) before its CTA counts itself in; the last CTA to finish writes, per destination
+// rank r, the payload {starts[r], starts[r+1]-starts[r]} (if payload_dst) and then the flag = *epoch
+// (st.release.sys) — data and flag leave from the same kernel, ordered by the fences of the threads that
+// wrote the data.  flag_dst == nullptr: nothing is published.
+struct SignalSpec {
+  unsigned long long* const* flag_dst = nullptr;   // [world] device table: this rank's flag word on every rank
+  int64_t* const* payload_dst = nullptr;           // [world] optional: two int64 per destination
+  const int64_t* starts = nullptr;                 // [world + 1] with payload_dst
+  const unsigned long long* epoch = nullptr;
+  unsigned int* done_ctr = nullptr;                // zero between launches
+  int world = 0;
+};
+
 // gather.cu
 // `seg_start`/`seg_dst` (device arrays, `segs` entries + 1 / `segs` entries) optionally scatter the output:
 // row k of segment g (seg_start[g] <= k < seg_start[g+1]) is stored at seg_dst[g] + (k - seg_start[g]) * d.
 template <typename T>
 cudaError_t launch_gather(const T* table, int64_t height, int64_t d, const int64_t* ids, int64_t n,
                           int64_t padding_idx, T* out, int32_t* status, cudaStream_t s,
-                          const int64_t* seg_start = nullptr, T* const* seg_dst = nullptr, int segs = 0);
+                          const int64_t* seg_start = nullptr, T* const* seg_dst = nullptr, int segs = 0,
+                          const SignalSpec& signal = SignalSpec());
 // with a scatter map only the first seg_start[segs] ids are looked up (a count known on the device alone)
 
 // segreduce.cu
@@ -135,6 +150,7 @@ struct UpdateArgs {
   const int64_t* shard_meta = nullptr;     // optional device pairs {row offset inside the destination, rows it accepts}
   int shards = 0;
   WaitSpec wait;                           // sharded path: the gradient rows come from other GPUs
+  SignalSpec signal;                       // sharded path: the merged rows go to other GPUs
   bool dst_aligned16 = true;               // caller's promise about the scatter destinations
 };
 template <typename T>

@@ -72,6 +72,7 @@ struct Params {
   int shards;
   const int64_t* shard_meta;  // optional pairs {rows to skip at the start of destination g, rows it accepts}
   WaitSpec wait;              // sharded owner side: `value` is stored by other GPUs; wait for their flags first
+  SignalSpec signal;          // sharded requester side: merged rows go to other GPUs; publish when all are stored
 };
 
 template <typename T>
@@ -315,23 +316,35 @@ __device__ __forceinline__ void close_chain(int c, int len, uint32_t key, uint32
 // a CTA then splits its adjusted range evenly over its groups.
 struct ChunkGeom {
   int n, chunk, slack;
+  int batch;     // rows per ring batch (timing only: the summation order does not depend on it)
 };
 
-// Rows per batch of the shared-memory ring (kRingStages batches in flight): sized so that the ring of a
-// CTA stays near 48 KB and three CTAs fit an SM for the common shapes.
+// The shared-memory ring holds kRingStages batches of `batch` rows (a launch parameter, <= kMaxBatch: the
+// batch loops are unrolled kMaxBatch times and predicated).
 constexpr int kRingStages = 3;
+constexpr int kMaxBatch = 4;
+constexpr int kRingTargetBytes = 48 * 1024;   // default ring size per CTA: three CTAs fit an SM for the common shapes
 template <typename T, UpdateOp OP, int NV, bool VEC>
 struct Ring {
   static constexpr int kVB = Epv<T, VEC>::value * static_cast<int>(sizeof(T));   // bytes per lane per vector
-  static constexpr int kParts = 1 + NumState<OP>::value;                         // gradient row + state rows
+  // state rows ride in the ring beside the gradient row while a slot stays <= 128 bytes per thread; wider
+  // shapes (>= 512 floats with moments) read them with plain loads when the segment closes
+  static constexpr bool kStateInRing = NumState<OP>::value > 0 && (1 + NumState<OP>::value) * NV <= 8;
+  static constexpr int kParts = kStateInRing ? 1 + NumState<OP>::value : 1;      // gradient row + state rows
   static constexpr int kSlotBytes = kParts * NV * kVB * kBlock;                  // one slot, whole CTA
-  static constexpr int kFit = (48 * 1024) / (kRingStages * kSlotBytes);
-  static constexpr int kBatch = kFit >= 4 ? 4 : (kFit >= 2 ? 2 : 1);
   // one more slot holds the state of the segment a group leaves open (single-state consumers only: for
   // Adam / Adagrad that slot would cost a resident CTA)
-  static constexpr bool kTailInRing = NumState<OP>::value == 1;
-  static constexpr int kSlots = kRingStages * kBatch + (kTailInRing ? 1 : 0);
-  static constexpr int kBytes = kSlots * kSlotBytes;
+  static constexpr bool kTailInRing = kStateInRing && NumState<OP>::value == 1;
+  static int batch_for(int target_bytes) {
+    const int fit = target_bytes / (kRingStages * kSlotBytes);
+    return fit >= 4 ? 4 : (fit >= 2 ? 2 : 1);
+  }
+  static size_t bytes_for(int batch) {
+    return static_cast<size_t>(kRingStages * batch + (kTailInRing ? 1 : 0)) * kSlotBytes;
+  }
+  static __device__ __forceinline__ uint32_t bytes_for_dev(int batch) {
+    return static_cast<uint32_t>(kRingStages * batch + (kTailInRing ? 1 : 0)) * kSlotBytes;
+  }
 };
 
 __device__ __forceinline__ void lds_vec(uint32_t addr, float (&v)[4]) {
@@ -359,19 +372,20 @@ constexpr uint32_t kCloses = 0x80000000u;    // the segment ends at this element
 constexpr uint32_t kDirect = 0x40000000u;    // ... and started inside this group's chunk: consumed on the spot
 
 template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
-__global__ void __launch_bounds__(kBlock, NV == 1 ? 3 : 2)
-k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ perm, ChunkGeom G,
-               const T* __restrict__ value, Params<T> P, Carry<T> C) {
+__device__ __forceinline__ void chunk_reduce_body(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ perm,
+                                                  const ChunkGeom& G, const T* __restrict__ value,
+                                                  const Params<T>& P, const Carry<T>& C) {
   constexpr int EPV = Epv<T, VEC>::value;
   constexpr int GPC = kBlock / LPR;
   constexpr int COLS = LPR * NV * EPV;
   constexpr int NS = NumState<OP>::value;
   using RG = Ring<T, OP, NV, VEC>;
-  constexpr int VB = RG::kVB, B = RG::kBatch, S = kRingStages;
+  constexpr int VB = RG::kVB, S = kRingStages;
+  const int B = G.batch;
   constexpr uint32_t kVecStride = kBlock * VB;                 // between the vectors of one slot
   constexpr uint32_t kPartStride = NV * kVecStride;            // between the parts (row, state rows) of one slot
   constexpr uint32_t kSlotStride = RG::kSlotBytes;
-  constexpr int kTailSlot = S * B;                             // state of the segment a group leaves open
+  const int kTailSlot = S * B;                                 // state of the segment a group leaves open
   using A = Arith<T>;
   const int n = G.n;
   const int stride = GPC * G.chunk;                            // nominal sorted elements per CTA
@@ -382,7 +396,7 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
   // ring[slot][part][vector][thread], filled by cp.async: a thread only ever touches its own column, so the
   // ring needs no barrier, only cp.async.wait_group
   const uint32_t ring = smem_addr(smem_raw) + tid * VB;
-  T* s_head = reinterpret_cast<T*>(smem_raw + RG::kBytes);    // [GPC][COLS]
+  T* s_head = reinterpret_cast<T*>(smem_raw + RG::bytes_for_dev(B));    // [GPC][COLS]
   T* s_tail = s_head + GPC * COLS;                            // [GPC][COLS]
   uint32_t* s_key = reinterpret_cast<uint32_t*>(s_tail + GPC * COLS);  // [win]
   uint32_t* s_pos = s_key + win;                              // [win] original position | kCloses | kDirect
@@ -391,6 +405,8 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
 
   const int cta = blockIdx.x, num_ctas = gridDim.x;
   const int d = P.d;
+  pdl_wait();
+  pdl_launch_dependents();
   wait_for_flags(P.wait.flags, P.wait.epoch, P.wait.world, P.wait.status);
   const int nom_s = cta * stride, nom_e = min(nom_s + stride, n);
   const int w0 = max(nom_s - 1, 0), w1 = min(nom_e + G.slack + 1, n);
@@ -514,9 +530,9 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
         const int i0 = gs + bi * B;
         const uint32_t stage_addr = ring + (bi % S) * (B * kSlotStride);
 #pragma unroll
-        for (int q = 0; q < B; ++q) {
+        for (int q = 0; q < kMaxBatch; ++q) {
           const int idx = i0 + q;
-          if (idx < ge) {
+          if (q < B && idx < ge) {
             const uint32_t pw = s_pos[idx - w0];
             const T* src = value + static_cast<int64_t>(pw & kPosMask) * d;
             const uint32_t slot_addr = stage_addr + q * kSlotStride;
@@ -525,7 +541,7 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
               const int col = col0 + (l + kk * LPR) * EPV;
               if (col < d) cp_async_s<VB>(slot_addr + kk * kVecStride, src + col);
             }
-            if (NS > 0 && (pw & kDirect)) fetch_state(slot_addr, K(idx));
+            if (RG::kStateInRing && (pw & kDirect)) fetch_state(slot_addr, K(idx));
           }
         }
       };
@@ -543,9 +559,9 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
         const int i0 = gs + bi * B;
         const uint32_t stage_addr = ring + (bi % S) * (B * kSlotStride);
 #pragma unroll
-        for (int q = 0; q < B; ++q) {
+        for (int q = 0; q < kMaxBatch; ++q) {
           const int idx = i0 + q;
-          if (idx < ge) {
+          if (q < B && idx < ge) {
             const uint32_t slot_addr = stage_addr + q * kSlotStride;
 #pragma unroll
             for (int kk = 0; kk < NV; ++kk) {
@@ -561,9 +577,13 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
             if (pw & kCloses) {   // the segment closes here
               if (pw & kDirect) {
                 const uint32_t key = K(idx);
-                RowState<T, OP, NV, EPV> st;
-                read_state(slot_addr, key, st);
-                apply_state<T, OP, LPR, NV, VEC>(P, key, static_cast<uint32_t>(idx), col0, l, acc, st);
+                if constexpr (RG::kStateInRing || NS == 0) {
+                  RowState<T, OP, NV, EPV> st;
+                  read_state(slot_addr, key, st);
+                  apply_state<T, OP, LPR, NV, VEC>(P, key, static_cast<uint32_t>(idx), col0, l, acc, st);
+                } else {
+                  consume<T, OP, LPR, NV, VEC>(P, key, static_cast<uint32_t>(idx), col0, l, acc);
+                }
               } else {  // first segment of the chunk, entered from the previous chunk
 #pragma unroll
                 for (int kk = 0; kk < NV; ++kk)
@@ -725,6 +745,15 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
   B200EMB_STAMP(6);
 }
 
+template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
+__global__ void __launch_bounds__(kBlock, NV == 1 ? 3 : 2)
+k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ perm, ChunkGeom G,
+               const T* __restrict__ value, Params<T> P, Carry<T> C) {
+  chunk_reduce_body<T, OP, LPR, NV, VEC>(skey, perm, G, value, P, C);   // every exit of the body is CTA-uniform
+  signal_peers(P.signal.flag_dst, P.signal.payload_dst, P.signal.starts, P.signal.epoch, P.signal.done_ctr,
+               P.signal.world);
+}
+
 // ------------------------------------------------------------------------------------------
 // Bit-exact order mode: one lane group per unique row, duplicates in input order.
 template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
@@ -816,7 +845,7 @@ cudaError_t launch_op(const SortedPlan& plan, const T* value, int64_t n, int64_t
                       cudaStream_t s) {
   Params<T> P{a.param, a.moment1, a.moment2, a.lr, a.beta1_pow, a.beta2_pow,
               a.beta1, a.beta2, a.epsilon, a.uidx, static_cast<int>(d),
-              static_cast<uint32_t>(height), a.shard_bounds, a.shard_dst, a.shards, a.shard_meta, a.wait};
+              static_cast<uint32_t>(height), a.shard_bounds, a.shard_dst, a.shards, a.shard_meta, a.wait, a.signal};
   Carry<T> C{reinterpret_cast<uint32_t*>(ws + L.off_cta_arrive),
              reinterpret_cast<T*>(ws + L.off_cta_head), reinterpret_cast<T*>(ws + L.off_cta_tail)};
   bool aligned = is_aligned16(value) && (a.shards > 0 || is_aligned16(a.param)) && a.dst_aligned16;
@@ -841,12 +870,24 @@ cudaError_t launch_op(const SortedPlan& plan, const T* value, int64_t n, int64_t
         const int c = ov ? std::atoi(ov) : 0;
         return (c >= kMinChunk && c <= kMaxChunk) ? c : 0;
       }();
-      const int chunk = chunk_override ? chunk_override : choose_chunk(n, GPC * 3);
+      static const int cps = [] {   // CTAs per SM the one-wave geometry aims at (tuning override, read once)
+        const char* ov = std::getenv("B200EMB_REDUCE_CPS");
+        const int c = ov ? std::atoi(ov) : 0;
+        return (c >= 1 && c <= 4) ? c : 3;
+      }();
+      static const int ring_target = [] {
+        const char* ov = std::getenv("B200EMB_RING_KB");
+        const int kb = ov ? std::atoi(ov) : 0;
+        return (kb >= 8 && kb <= 160) ? kb * 1024 : kRingTargetBytes;
+      }();
+      const int chunk = chunk_override ? chunk_override : choose_chunk(n, GPC * cps);
       const int ctas = static_cast<int>(ceil_div(n, static_cast<int64_t>(GPC) * chunk));
       const int slack = std::min(kBoundarySlack, GPC * chunk / 2);
-      const size_t smem = Ring<T, OP, NV, VEC>::kBytes + sizeof(T) * 2 * GPC * COLS +
+      using RG = Ring<T, OP, NV, VEC>;
+      const int batch = RG::batch_for(ring_target);
+      const size_t smem = RG::bytes_for(batch) + sizeof(T) * 2 * GPC * COLS +
                           sizeof(uint32_t) * 2 * (GPC * chunk + slack + 2);
-      const ChunkGeom G{ni, chunk, slack};
+      const ChunkGeom G{ni, chunk, slack, batch};
       auto kern = k_chunk_reduce<T, OP, LPR, NV, VEC>;
       // opt in to > 48 KB of dynamic shared memory once per device (the attribute is per device)
       static std::atomic<unsigned long long> attr_done{0};
@@ -860,7 +901,8 @@ cudaError_t launch_op(const SortedPlan& plan, const T* value, int64_t n, int64_t
         }
         attr_done.fetch_or(bit, std::memory_order_relaxed);
       }
-      kern<<<ctas, kBlock, smem, s>>>(plan.keys, plan.perm, G, value, P, C);
+      err = launch_row_kernel(kern, ctas, kBlock, smem, s, plan.keys, plan.perm, G, value, P, C);
+      return;
     }
     err = cudaGetLastError();
   });

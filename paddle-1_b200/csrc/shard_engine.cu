@@ -8,6 +8,7 @@
 //
 // One engine per rank (one GPU).  Every rank owns one peer-visible block (CUDA IPC between processes, plain
 // peer pointers inside one process) that the OTHER ranks' kernels store into over NVLink:
+//     header    int64 [8]            {magic, G, capacities, D}: connect() refuses ranks whose layout differs
 //     ids_in    int64 [G][cap_src]   unique local rows requested by each source rank (its own region)
 //     meta_in   int64 [G][2]         {count, offset of these rows in the requester's unique list}
 //     meta_back int64 [G][2]         per owner: {where this rank's rows start in the owner's compact list, rows accepted}
@@ -20,11 +21,11 @@
 //     lookup   k_send_ids        unique local rows -> owners' ids_in, meta, flag        [NVLink 8 B / unique id]
 //              k_collect_ids     (owner) wait ids flags; compact into recv rows, pad, scatter maps
 //              sort plan of the received rows (side stream: only the update needs it)
-//              k_gather          (owner) rows of the shard -> requesters' uvals           [NVLink 4D B / unique id]
-//              k_signal          meta_back + rows flag
+//              k_gather          (owner) rows of the shard -> requesters' uvals, then meta_back + rows flag
+//                                from the same kernel (every thread fences its stores)    [NVLink 4D B / unique id]
 //              k_permute_rows    wait rows flags; expand unique rows to batch order (= merge_ids)
-//     update   k_chunk_reduce<MergeAdd>  local duplicate reduction -> owners' grads_in    [NVLink 4D B / unique id]
-//              k_signal          gradient flag
+//     update   k_chunk_reduce<MergeAdd>  local duplicate reduction -> owners' grads_in, then the gradient flag
+//                                from the same kernel                                      [NVLink 4D B / unique id]
 //              k_chunk_reduce<Sgd|Adam>  (owner) wait gradient flags; fused update of the shard
 // Buffers are single: the step's own data dependencies order their reuse (a rank cannot send the ids of step
 // i+1 before it has expanded the rows of step i, which every owner sent after collecting the ids of step i, ...).
@@ -46,13 +47,15 @@ constexpr int kMaxWorld = 64;
 constexpr int kPrepSlots = 4;
 
 struct BlockLayout {
-  size_t off_ids_in, off_meta_in, off_meta_back, off_flags, off_uvals, off_grads_in, total;
+  size_t off_header, off_ids_in, off_meta_in, off_meta_back, off_flags, off_uvals, off_grads_in, total;
 };
+constexpr long long kBlockMagic = 0x4232303045534831LL;   // every rank's block must have the same layout
 
 BlockLayout make_block(int world, int64_t cap_src, int64_t cap_ids, int64_t cap_recv, int64_t d) {
   BlockLayout B{};
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes); return o; };
+  B.off_header = take(sizeof(long long) * 8);   // {magic, world, cap_src, cap_ids, cap_recv, d}
   B.off_ids_in = take(sizeof(int64_t) * world * cap_src);
   B.off_meta_in = take(sizeof(int64_t) * world * 2);
   B.off_meta_back = take(sizeof(int64_t) * world * 2);
@@ -104,7 +107,7 @@ struct b200emb_shard {
   int64_t* seg_start = nullptr;          // [world + 1]
   float** seg_dst = nullptr;             // [world]
   unsigned long long* epoch = nullptr;   // the step counter, advanced by k_send_ids
-  unsigned int* done_ctr = nullptr;      // last-CTA detection of k_send_ids
+  unsigned int* done_ctr = nullptr;      // [3] last-CTA detection of k_send_ids / owner gather / local MergeAdd
   int32_t* status = nullptr;
   char* owner_ws = nullptr;
   size_t owner_ws_bytes = 0, prep_ws_bytes = 0;
@@ -252,6 +255,10 @@ int b200emb_shard_create(int world, int rank, int64_t height, int64_t d, int opt
   sh->opened.assign(world, false);
   cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&sh->block), sh->L.total);
   if (e == cudaSuccess) e = cudaMemset(sh->block, 0, sh->L.total);
+  if (e == cudaSuccess) {
+    const long long hdr[8] = {kBlockMagic, world, sh->cap_src, sh->cap_ids, sh->cap_recv, d, 0, 0};
+    e = cudaMemcpy(sh->block + sh->L.off_header, hdr, sizeof(hdr), cudaMemcpyHostToDevice);
+  }
   // private memory: tables, compact list, per-slot plan outputs, workspaces
   // a workspace good for ANY n <= n_max: the sort's tile size depends on n, so take the larger of the two regimes
   const auto ws_upto = [&](int64_t n_max) {
@@ -289,7 +296,7 @@ int b200emb_shard_create(int world, int rank, int64_t height, int64_t d, int opt
   sh->seg_start = carve<int64_t>(cur, w + 1);
   sh->seg_dst = carve<float*>(cur, w);
   sh->epoch = carve<unsigned long long>(cur, 1);
-  sh->done_ctr = carve<unsigned int>(cur, 1);
+  sh->done_ctr = carve<unsigned int>(cur, 3);
   sh->status = carve<int32_t>(cur, 1);
   sh->owner_ws = cur; cur += align_up(sh->owner_ws_bytes);
   for (int s = 0; s < kPrepSlots; ++s) {
@@ -317,6 +324,16 @@ void* b200emb_shard_block(b200emb_shard_t* sh) { return sh ? sh->block : nullptr
 static int finish_connect(b200emb_shard* sh) {
   const int w = sh->world, me = sh->rank;
   const BlockLayout& L = sh->L;
+  for (int g = 0; g < w; ++g) {   // pointers into a peer's block are computed with THIS rank's layout: it must match
+    long long hdr[8] = {0};
+    if (cudaMemcpy(hdr, sh->peer[g] + L.off_header, sizeof(hdr), cudaMemcpyDeviceToHost) != cudaSuccess) {
+      cudaGetLastError();
+      return B200EMB_E_CUDA;
+    }
+    if (hdr[0] != kBlockMagic || hdr[1] != w || hdr[2] != sh->cap_src || hdr[3] != sh->cap_ids ||
+        hdr[4] != sh->cap_recv || hdr[5] != sh->d)
+      return B200EMB_E_INVALID;   // create() was called with different sizes on that rank
+  }
   std::vector<void*> h(8 * static_cast<size_t>(w));
   for (int g = 0; g < w; ++g) {
     char* pb = sh->peer[g];
@@ -404,11 +421,18 @@ int b200emb_shard_lookup_phases(b200emb_shard_t* sh, int slot, float* out, void*
     if ((e = cudaEventRecord(sh->ev_plan, sh->side)) != cudaSuccess) return fail(e);
   }
   if (first <= 2 && 2 <= last) {
+    // the rows and the rows flag leave from the same kernel: every thread fences its peer stores before the last
+    // CTA raises the flags (and tells each requester where its rows sit in this owner's compact list)
+    SignalSpec sg;
+    sg.flag_dst = sh->T.flag_rows;
+    sg.payload_dst = sh->T.meta_back;
+    sg.starts = sh->seg_start;
+    sg.epoch = sh->epoch;
+    sg.done_ctr = sh->done_ctr + 1;
+    sg.world = w;
     e = launch_gather<float>(sh->shard, sh->hs, sh->d, sh->recv_local, sh->cap_recv, -1, nullptr, nullptr, s,
-                             sh->seg_start, sh->seg_dst, w);
+                             sh->seg_start, sh->seg_dst, w, sg);
     if (e != cudaSuccess) return fail(e);
-    k_signal<<<1, ((w + 31) / 32) * 32, 0, s>>>(w, sh->T.meta_back, sh->seg_start, sh->T.flag_rows, sh->epoch);
-    if ((e = cudaGetLastError()) != cudaSuccess) return fail(e);
   }
   if (first <= 3 && 3 <= last && p.n > 0) {
     const Workspace PW = make_workspace(p.n, 1, 4);
@@ -456,12 +480,17 @@ int b200emb_shard_update_phases(b200emb_shard_t* sh, int slot, const float* d_ou
       a.shard_meta = reinterpret_cast<const int64_t*>(sh->block + L.off_meta_back);
       a.shards = w;
       a.dst_aligned16 = (sh->d % 4) == 0;
+      a.signal.flag_dst = sh->T.flag_grads;      // merged rows and their flag leave from the same kernel
+      a.signal.epoch = sh->epoch;
+      a.signal.done_ctr = sh->done_ctr + 2;
+      a.signal.world = w;
       const SortedPlan plan = plan_view(p.n, sh->plan_h, p.ws, PW);
       e = launch_update<float>(plan, d_out, p.n, sh->d, sh->plan_h, a, false, p.ws, PW, sh->status, s);
       if (e != cudaSuccess) return fail(e);
+    } else {   // an empty batch still has to tell the owners that nothing is coming
+      k_signal<<<1, ((w + 31) / 32) * 32, 0, s>>>(w, nullptr, nullptr, sh->T.flag_grads, sh->epoch);
+      if ((e = cudaGetLastError()) != cudaSuccess) return fail(e);
     }
-    k_signal<<<1, ((w + 31) / 32) * 32, 0, s>>>(w, nullptr, nullptr, sh->T.flag_grads, sh->epoch);
-    if ((e = cudaGetLastError()) != cudaSuccess) return fail(e);
   }
   if (first <= 1 && 1 <= last) {
     if ((e = cudaStreamWaitEvent(s, sh->ev_plan, 0)) != cudaSuccess) return fail(e);

@@ -87,9 +87,11 @@ def test_engine_ranks_on_one_gpu(capi, world, optimizer):
     ids_d = [[torch.from_numpy(i).to(dev) for i in b] for b in batches]
     g_d = [[torch.from_numpy(g).to(dev) for g in gs] for gs in grads]
 
+    main = torch.cuda.current_stream(dev)
+
     def prepare(step):
+        side.wait_stream(main)
         with torch.cuda.stream(side):
-            side.wait_stream(torch.cuda.current_stream(dev))
             for r in range(world):
                 eng[r].prepare(step % 4, ids_d[step][r])
 
@@ -123,10 +125,18 @@ def test_engine_ranks_on_one_gpu(capi, world, optimizer):
             wp, w1, w2 = ref.copy(), rm1.copy(), rm2.copy()
             oracle.adam_sparse(wp, w1, w2, all_ids[ok], all_g[ok], np.array([0.05], np.float32),
                                np.array([0.9], np.float32), np.array([0.999], np.float32))
-            np.testing.assert_allclose(after, wp, rtol=2e-5, atol=1e-7)
+            # Adam divides by sqrt(m2): where a merged gradient nearly cancels, the rounding of the fast-mode
+            # tree moves the parameter by a visible fraction of one step (lr_t * m1 / sqrt(m2) is O(lr)), so the
+            # parameters are held to a small fraction of outliers and the moments (linear in g) to the bound
+            diff = np.abs(after - wp)
+            assert (diff > 2e-5 * np.abs(wp) + 1e-7).mean() < 1e-5 and diff.max() < 0.1
             rm1 = _unshard([m.cpu().numpy() for m in m1], v)
             rm2 = _unshard([m.cpu().numpy() for m in m2], v)
-            np.testing.assert_allclose(rm1, w1, rtol=2e-5, atol=1e-9)
+            _, l1 = oracle.merge_add(all_ids[ok], np.abs(all_g[ok]), truth=True)
+            rows_u = np.unique(all_ids[ok])
+            bound = 1e-6 * np.abs(w1)
+            bound[rows_u] += 1e-6 * 0.1 * l1
+            assert (np.abs(rm1 - w1) <= bound + 1e-30).all()
         ref = after          # the next step starts from what the engine left (errors do not accumulate in the check)
     for r in range(world):
         st = int(eng[r].status.item())
@@ -187,13 +197,13 @@ def _worker(rank, world, port, q, steps, n, slow_rank):
         for s in range(steps):
             torch.cuda.current_stream(dev).wait_stream(side)
             if s + 1 < steps:
+                side.wait_stream(torch.cuda.current_stream(dev))
                 with torch.cuda.stream(side):
-                    side.wait_stream(torch.cuda.current_stream(dev))
                     eng.prepare((s + 1) % 4, ids_d[s + 1])
-            if rank == slow_rank:
+            if slow_rank is not None and rank == slow_rank:
                 torch.cuda._sleep(int(3e6))          # ~1.5 ms: this rank lags, the others run ahead
             outs.append(eng.lookup(s % 4))
-            if rank == (slow_rank + 1) % world:
+            if slow_rank is not None and rank == (slow_rank + 1) % world:
                 torch.cuda._sleep(int(2e6))
             eng.update(s % 4, g_d[s], lr)
         torch.cuda.synchronize()
@@ -206,8 +216,9 @@ def _worker(rank, world, port, q, steps, n, slow_rank):
         dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("slow_rank", [None, 1], ids=["even", "skewed"])
 @pytest.mark.parametrize("world", [2, 4, 8])
-def test_engine_one_process_per_gpu(capi, world):
+def test_engine_one_process_per_gpu(capi, world, slow_rank):
     if torch.cuda.device_count() < world:
         pytest.skip("needs %d GPUs (run with gpurun --gpus %d)" % (world, world))
     import torch.multiprocessing as mp
@@ -215,7 +226,7 @@ def test_engine_one_process_per_gpu(capi, world):
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, q, steps, n, 1)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q, steps, n, slow_rank)) for r in range(world)]
     for p in procs:
         p.start()
     got = sorted([q.get(timeout=600) for _ in range(world)], key=lambda t: t[0])
@@ -232,8 +243,17 @@ def test_engine_one_process_per_gpu(capi, world):
         dout = np.concatenate([g[4][s_] for g in got])
         # forward of step s_ saw the table after s_ updates: within the accumulated reordering bound of the truth
         for g in got:
-            o = g[5][s_]
-            assert (np.abs(o - truth[g[3][s_]]) <= bound_acc[g[3][s_]] + 1e-6 * np.abs(truth[g[3][s_]]) + 1e-30).all(), s_
+            o, i_ = g[5][s_], g[3][s_]
+            bad = np.abs(o - truth[i_]) > bound_acc[i_] + 1e-6 * np.abs(truth[i_]) + 1e-30
+            if bad.any():     # say what the rows look like instead: another step's ids? the untouched table?
+                alt = {}
+                for t_ in range(steps):
+                    alt["ids_of_step_%d" % t_] = float((np.abs(o - truth[g[3][t_]]) < 1e-3).all(axis=1).mean())
+                alt["initial_table_same_ids"] = float((o == ref[i_]).all(axis=1).mean())
+                raise AssertionError("step %d rank %d: %d of %d elements off (max %.3g); rows owned by ranks %s; "
+                                     "fraction of rows matching %s" % (
+                                         s_, g[0], int(bad.sum()), bad.size, float(np.abs(o - truth[i_]).max()),
+                                         sorted(set((i_[bad.any(axis=1)] % world).tolist())), alt))
         rows, merged = oracle.merge_add(ids, dout, truth=True)
         _, l1 = oracle.merge_add(ids, np.abs(dout), truth=True)
         truth[rows] -= 0.05 * merged
