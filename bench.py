@@ -315,13 +315,14 @@ def extra_config(torch, capi, synth, stepbench, name, dev, peak, steps):
     return res
 
 
-def e2e_opkernel(torch, pkg, table_np, ids_h, dout_h, n, d, v, steps):
+def e2e_opkernel(torch, pkg, table_np, ids_h, dout_h, n, d, v, steps, fused):
     """The same step through the drop-in boundary a Fluid program reaches: Operator.run of the registered
     lookup_table -> lookup_table_grad (is_sparse) -> sgd CUDA OpKernels (paddle-1_b200/fluid/, REGISTER_OP_CUDA_KERNEL)
     on host numpy batches: feed (H2D) ids and Out@GRAD, run the three ops, fetch Out (D2H), synchronously like
     Executor::Run does (framework/executor.cc:332-340)."""
     from importlib import import_module
     core = import_module("paddle1_b200.fluid_lite")
+    core.set_fused(fused)
     place = core.CUDAPlace(0)
     scope = core.Scope()
     scope.var("W").get_tensor().set(table_np, place)
@@ -346,7 +347,10 @@ def e2e_opkernel(torch, pkg, table_np, ids_h, dout_h, n, d, v, steps):
     for i in range(steps):
         one(i)
     el = time.perf_counter() - t0
+    core.set_fused(False)
     return {"value": n * steps / el, "unit": UNIT, "ms_per_step": el / steps * 1e3, "steps": steps,
+            "mode": "fused (FLAGS_b200emb_fused: gradient stays on the device, sort plan started by the forward op)"
+                    if fused else "materialised (rows written into the SelectedRows like the reference)",
             "h2d_bytes_per_step": n * 8 + n * d * 4, "d2h_bytes_per_step": n * d * 4,
             "api": "fluid_lite.Operator('lookup_table' | 'lookup_table_grad' | 'sgd').run(scope, CUDAPlace(0)) — the "
                    "registered OpKernel wrappers; pageable numpy feeds, synchronous feed/run/fetch"}
@@ -447,7 +451,9 @@ def run_single(args):
     # ---- end to end: host buffers, H2D of ids+dOut and D2H of Out inside the timed region ---------
     e2e = run_e2e(torch, capi, table, lr, ids_h, dout_h, n, d, v, status, max(20, min(args.steps, 200)))
     try:
-        e2e_ok = e2e_opkernel(torch, pkg, table_np, ids_h, dout_h, n, d, v, max(10, min(args.steps, 50)))
+        e2e_ok = e2e_opkernel(torch, pkg, table_np, ids_h, dout_h, n, d, v, max(10, min(args.steps, 50)), True)
+        e2e_ok["materialised_mode"] = e2e_opkernel(torch, pkg, table_np, ids_h, dout_h, n, d, v,
+                                                   max(10, min(args.steps, 50)), False)
     except Exception as e:  # the wrappers are a separate library: report, do not hide
         e2e_ok = {"error": str(e)[:300]}
 

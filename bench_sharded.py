@@ -167,24 +167,52 @@ def measure(pkg, tab, zipf, n, d, rank, world, dev, steps, warm, lr, want_e2e, u
            # bytes this rank sends over NVLink per step: ids + gradient rows of the rows it does not own, and the
            # rows it returns to the other requesters (about as many as it receives from them)
            "nvlink_out_bytes": (u_local - own) * (8 + 4 * d) + (recv_rows - own) * 4 * d}
-    # per-phase device times on rank 0 (eager, a few extra untimed steps)
-    tab.phase_events = []
-    eager = Stepper(tab, wl, lr, dev, False)
-    eager.run(4)
-    torch.cuda.synchronize(dev)
-    phases = {}
-    for name, a0, a1 in tab.phase_events:
-        phases[name] = phases.get(name, 0.0) + a0.elapsed_time(a1) / 4 * 1e3
-    tab.phase_events = None
-    res["phases_us"] = {k: round(x, 1) for k, x in phases.items()}
+    # per-kernel-group device times on rank 0: eager launches, one engine phase per call, CUDA events around each
+    # (consumer phases include the wait for the peers' flags, so rank skew shows up there)
+    res["phases_us"] = phase_breakdown(tab.engine, wl, lr, dev, 6)
     dist.barrier()
     if want_e2e:
         res["e2e"] = e2e_pipeline(tab, wl, lr, dev, world, max(8, min(steps, 40)))
     tab.engine.destroy()
     tab.peer = False
-    del wl, st, eager
+    del wl, st
     torch.cuda.empty_cache()
     return res
+
+
+def phase_breakdown(eng, wl, lr, dev, steps):
+    names = ["prepare: sort plan + de-duplication (side stream, one batch ahead)", "send ids to owners",
+             "collect ids (waits for every source) + fork owner sort plan", "owner gather -> requesters, rows flags",
+             "expand to batch order (waits for every owner)", "local MergeAdd -> owners, gradient flags",
+             "owner fused update (waits for every source, joins owner sort plan)"]
+    main = torch.cuda.current_stream(dev)
+    side = torch.cuda.Stream(dev)
+    acc = [0.0] * len(names)
+    evs = []
+    dist.barrier()
+    for i in range(steps + 2):
+        b = i % N_ROTATE
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(9)]
+        side.wait_stream(main)
+        with torch.cuda.stream(side):
+            ev[0].record(side)
+            eng.prepare(b, wl.ids[b])
+            ev[1].record(side)
+        main.wait_stream(side)
+        ev[2].record(main)
+        for ph in range(4):
+            eng.lookup(b, wl.out[b], phases=(ph, ph))
+            ev[3 + ph].record(main)
+        for ph in range(2):
+            eng.update(b, wl.dout[b], lr, phases=(ph, ph))
+            ev[7 + ph].record(main)
+        evs.append(ev)
+    torch.cuda.synchronize(dev)
+    for ev in evs[2:]:
+        acc[0] += ev[0].elapsed_time(ev[1])
+        for k in range(6):
+            acc[1 + k] += ev[2 + k].elapsed_time(ev[3 + k])
+    return {n_: round(a / steps * 1e3, 1) for n_, a in zip(names, acc)}
 
 
 def e2e_pipeline(tab, wl, lr, dev, world, steps):

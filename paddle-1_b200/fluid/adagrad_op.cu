@@ -51,16 +51,17 @@ class AdagradOpB200Kernel : public framework::OpKernel<T> {
       auto* grad = ctx.Input<framework::SelectedRows>("Grad");
       PADDLE_ENFORCE_EQ(param, param_out);          // adagrad_op.h:63-66
       PADDLE_ENFORCE_EQ(moment, moment_out);
-      const int64_t n = static_cast<int64_t>(grad->rows().size());
-      if (n == 0) return;
-      const int64_t height = grad->height(), d = grad->value().numel() / n;
-      PADDLE_ENFORCE_EQ(height, param_out->dims()[0]);
-      framework::Tensor ws;
-      size_t ws_bytes = 0;
-      void* wsp = b200::Workspace(&ws, n, d, sizeof(T), ctx.GetPlace(), &ws_bytes);
-      B200EMB_CHECK(AdagradApi<T>::fn(p_out, m_out, height, d, grad->rows().CUDAData(ctx.GetPlace()),
-                                      grad->value().data<T>(), n, lr->data<T>(), epsilon, wsp, ws_bytes,
-                                      b200::Flags(), nullptr, stream));
+      const int device = boost::get<platform::CUDAPlace>(ctx.GetPlace()).device;
+      const b200::SparseGradView g = b200::ViewSparseGrad<T>(device, ctx.GetPlace(), grad);
+      if (g.n == 0) return;
+      PADDLE_ENFORCE_EQ(g.height, param_out->dims()[0]);
+      b200::UpdateWorkspace w;
+      b200::PrepareWorkspace(&w, g, sizeof(T), ctx.GetPlace(), stream);
+      b200::StatusWord status(ctx.GetPlace(), stream);
+      B200EMB_CHECK(AdagradApi<T>::fn(p_out, m_out, g.height, g.d, g.rows, static_cast<const T*>(g.value), g.n,
+                                      lr->data<T>(), epsilon, w.ptr, w.bytes, w.flags, status.get(), stream));
+      b200::SideTable::Instance().Release(device, g.plan);
+      status.Enforce("adagrad");
     } else {
       PADDLE_THROW("Unsupported Variable Type of Grad");
     }

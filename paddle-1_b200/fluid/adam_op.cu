@@ -64,23 +64,24 @@ class AdamOpB200Kernel : public framework::OpKernel<T> {
                                              p_out, n);
     } else if (grad_var->IsType<framework::SelectedRows>()) {
       auto& grad = Ref(ctx.Input<framework::SelectedRows>("Grad"), "Must set Grad");
-      const int64_t n = static_cast<int64_t>(grad.rows().size());
-      if (n == 0) return;                                                      // adam_op.h:285-288
+      const int device = boost::get<platform::CUDAPlace>(ctx.GetPlace()).device;
+      const b200::SparseGradView g = b200::ViewSparseGrad<T>(device, ctx.GetPlace(), &grad);
+      if (g.n == 0) return;                                                    // adam_op.h:285-288
       // the sparse update is in place: only touched rows change (lazy Adam), so outputs must alias
       // their inputs, as python/paddle/fluid/optimizer.py:562-566 wires them
       PADDLE_ENFORCE_EQ(p_out, param.template data<T>(), "sparse adam needs ParamOut == Param");
       PADDLE_ENFORCE_EQ(m1_out, mom1.template data<T>(), "sparse adam needs Moment1Out == Moment1");
       PADDLE_ENFORCE_EQ(m2_out, mom2.template data<T>(), "sparse adam needs Moment2Out == Moment2");
-      const int64_t height = grad.height(), d = grad.value().numel() / n;
-      PADDLE_ENFORCE_EQ(height, param.dims()[0]);
-      const int64_t* rows = grad.rows().CUDAData(ctx.GetPlace());
-      framework::Tensor ws;
-      size_t ws_bytes = 0;
-      void* wsp = b200::Workspace(&ws, n, d, sizeof(T), ctx.GetPlace(), &ws_bytes);
-      B200EMB_CHECK(b200::Api<T>::adam(p_out, m1_out, m2_out, height, d, rows, grad.value().template data<T>(), n,
+      PADDLE_ENFORCE_EQ(g.height, param.dims()[0]);
+      b200::UpdateWorkspace w;
+      b200::PrepareWorkspace(&w, g, sizeof(T), ctx.GetPlace(), stream);
+      b200::StatusWord status(ctx.GetPlace(), stream);
+      B200EMB_CHECK(b200::Api<T>::adam(p_out, m1_out, m2_out, g.height, g.d, g.rows, static_cast<const T*>(g.value), g.n,
                                        lr.template data<T>(), beta1_pow.template data<T>(),
-                                       beta2_pow.template data<T>(), beta1, beta2, epsilon, wsp, ws_bytes,
-                                       b200::Flags(), nullptr, stream));
+                                       beta2_pow.template data<T>(), beta1, beta2, epsilon, w.ptr, w.bytes,
+                                       w.flags, status.get(), stream));
+      b200::SideTable::Instance().Release(device, g.plan);
+      status.Enforce("adam");
     } else {
       PADDLE_THROW("Variable type not supported by adam_op");
     }

@@ -6,6 +6,7 @@
 #include "b200emb.h"
 #include "paddle/fluid/framework/op_registry.h"
 #include "paddle/fluid/framework/selected_rows.h"
+#include "b200_side_table.h"
 
 namespace paddle {
 namespace operators {
@@ -25,6 +26,60 @@ inline void* Workspace(framework::Tensor* ws, int64_t n, int64_t d, size_t elem,
   *bytes = b200emb_workspace_bytes(n, d, static_cast<int64_t>(elem));
   return ws->mutable_data<uint8_t>(framework::make_ddim({static_cast<int64_t>(*bytes)}), place);
 }
+
+// Workspace + flags for a consumer of a sparse gradient: the plan the forward op started (fused mode) once the
+// main stream has been told to wait for it, else a fresh temporary from the framework allocator.
+struct UpdateWorkspace {
+  framework::Tensor tmp;
+  void* ptr = nullptr;
+  size_t bytes = 0;
+  unsigned flags = 0;
+};
+inline void PrepareWorkspace(UpdateWorkspace* w, const SparseGradView& g, size_t elem, const platform::Place& place,
+                             cudaStream_t stream) {
+  w->flags = Flags();
+  if (g.plan && !(w->flags & B200EMB_DETERMINISTIC) && g.plan->bytes >= b200emb_workspace_bytes(g.n, g.d, elem)) {
+    PADDLE_ENFORCE(cudaStreamWaitEvent(stream, g.plan->done, 0) == cudaSuccess);
+    w->ptr = g.plan->ws.data<uint8_t>();
+    w->bytes = g.plan->bytes;
+    w->flags |= B200EMB_PLAN_READY;
+  } else {
+    w->ptr = Workspace(&w->tmp, g.n, g.d, elem, place, &w->bytes);
+  }
+}
+
+// The reference enforces 0 <= id < height on the host (lookup_table_op.h:59-60, sgd_op.h:75-76) or traps the
+// device (platform/assert.h:20-29).  The kernels here skip such rows and raise a bit in a per-device status
+// word instead; with FLAGS_b200emb_check_ids (env B200EMB_CHECK_IDS=1) every op reads that word back after
+// its launch — one stream sync per op, like FLAGS_benchmark (framework/operator.cc:722-724) — and enforces.
+inline bool CheckIds() {
+  static const bool on = [] {
+    const char* e = std::getenv("B200EMB_CHECK_IDS");
+    return e && e[0] && e[0] != '0';
+  }();
+  return on;
+}
+class StatusWord {
+ public:
+  StatusWord(const platform::Place& place, cudaStream_t stream) : stream_(stream) {
+    if (!CheckIds()) return;
+    word_ = t_.mutable_data<int32_t>(framework::make_ddim({1}), place);
+    PADDLE_ENFORCE(cudaMemsetAsync(word_, 0, sizeof(int32_t), stream_) == cudaSuccess);
+  }
+  int32_t* get() { return word_; }
+  void Enforce(const char* op) {
+    if (!word_) return;
+    int32_t h = 0;
+    PADDLE_ENFORCE(cudaMemcpyAsync(&h, word_, sizeof(h), cudaMemcpyDeviceToHost, stream_) == cudaSuccess);
+    PADDLE_ENFORCE(cudaStreamSynchronize(stream_) == cudaSuccess);
+    PADDLE_ENFORCE_EQ(h, 0, "%s: an id / row is outside [0, height) (status %d)", op, h);
+  }
+
+ private:
+  framework::Tensor t_;
+  int32_t* word_ = nullptr;
+  cudaStream_t stream_;
+};
 
 #define B200EMB_CHECK(call)                                                              \
   do {                                                                                   \

@@ -25,8 +25,16 @@ class LookupTableB200Kernel : public framework::OpKernel<T> {
     output_t->set_lod(ids_t->lod());                      // LoD forwarded (lookup_table_op.cc:46-49)
     T* out = output_t->mutable_data<T>(context.GetPlace());
     if (K == 0) return;
+    auto stream = context.cuda_device_context().stream();
+    b200::StatusWord status(context.GetPlace(), stream);
     B200EMB_CHECK(b200::Api<T>::lookup(table_t->data<T>(), V, D, ids_t->data<int64_t>(), K, padding_idx, out,
-                                       nullptr, context.cuda_device_context().stream()));
+                                       status.get(), stream));
+    // fused mode: the sparse gradient of this lookup will be sorted by these very ids — start that now, on the
+    // side stream, so the optimizer op finds the plan ready (b200_side_table.h)
+    if (b200::SideTable::Instance().fused() && context.Attr<bool>("is_sparse"))
+      b200::SideTable::Instance().StartPlan(boost::get<platform::CUDAPlace>(context.GetPlace()).device,
+                                            context.GetPlace(), ids_t->data<int64_t>(), K, V, D, sizeof(T), stream);
+    status.Enforce("lookup_table");
   }
 };
 
@@ -46,6 +54,19 @@ class LookupTableGradB200Kernel : public framework::OpKernel<T> {
       auto* d_table = context.Output<SelectedRows>(framework::GradVarName("W"));
       auto* rows = d_table->mutable_rows();
       rows->resize(static_cast<size_t>(K));
+      if (b200::SideTable::Instance().fused()) {
+        // zero copy: the gradient IS (Ids, dOut); consumers read both through the side table, rows() keeps
+        // its size only (b200_side_table.h).  The value tensor shares dOut's memory.
+        d_table->mutable_value()->ShareDataWith(*d_output);
+        d_table->mutable_value()->Resize({K, D});
+        d_table->set_height(V);
+        b200::SparseGradRecord rec;
+        rec.ids = ids->data<int64_t>();
+        rec.value = d_output->data<T>();
+        rec.n = K; rec.d = D; rec.height = V;
+        b200::SideTable::Instance().Bind(boost::get<platform::CUDAPlace>(context.GetPlace()).device, d_table, rec);
+        return;
+      }
       auto* d_table_value = d_table->mutable_value();
       d_table_value->Resize({K, D});
       T* value = d_table_value->mutable_data<T>(context.GetPlace());

@@ -13,6 +13,7 @@
 #include "paddle/fluid/framework/lod_tensor.h"
 #include "paddle/fluid/framework/op_registry.h"
 #include "paddle/fluid/framework/selected_rows.h"
+#include "b200_side_table.h"
 
 namespace fw = paddle::framework;
 namespace pf = paddle::platform;
@@ -232,6 +233,12 @@ int fl_op_run(void* s, const char* type, const char* inputs, const char* outputs
   PADDLE_ENFORCE(e == cudaSuccess, "CUDA error after %s: %s", type, cudaGetErrorString(e));
   return 0;
   FL_CATCH(-1)
+}
+
+// FLAGS_b200emb_fused of a real tree: sparse gradients stay on the device between our ops (b200_side_table.h)
+int fl_set_fused(int on) {
+  paddle::operators::b200::SideTable::Instance().SetFused(on != 0);
+  return 0;
 }
 
 int fl_num_registered_kernels(const char* type) {

@@ -37,18 +37,18 @@ class SGDOpB200Kernel : public framework::OpKernel<T> {
     } else if (grad_var->IsType<framework::SelectedRows>()) {
       PADDLE_ENFORCE_EQ(param, param_out);                       // in place, sgd_op.cu:84
       auto* grad = ctx.Input<framework::SelectedRows>("Grad");
-      const int64_t n = static_cast<int64_t>(grad->rows().size());
-      if (n == 0) return;                                        // sgd_op.h:56-58 (the CUDA file forgot it)
-      const int64_t height = grad->height();
-      PADDLE_ENFORCE_EQ(height, param_out->dims()[0]);           // sgd_op.h:60-62
-      const int64_t d = grad->value().numel() / n;
-      PADDLE_ENFORCE_EQ(d, param_out->numel() / height);
-      const int64_t* rows = grad->rows().CUDAData(ctx.GetPlace());
-      framework::Tensor ws;
-      size_t ws_bytes = 0;
-      void* wsp = b200::Workspace(&ws, n, d, sizeof(T), ctx.GetPlace(), &ws_bytes);
-      B200EMB_CHECK(b200::Api<T>::sgd(param_out->data<T>(), height, d, rows, grad->value().data<T>(), n,
-                                      learning_rate->data<T>(), wsp, ws_bytes, b200::Flags(), nullptr, stream));
+      const int device = boost::get<platform::CUDAPlace>(ctx.GetPlace()).device;
+      const b200::SparseGradView g = b200::ViewSparseGrad<T>(device, ctx.GetPlace(), grad);
+      if (g.n == 0) return;                                      // sgd_op.h:56-58 (the CUDA file forgot it)
+      PADDLE_ENFORCE_EQ(g.height, param_out->dims()[0]);         // sgd_op.h:60-62
+      PADDLE_ENFORCE_EQ(g.d, param_out->numel() / g.height);
+      b200::UpdateWorkspace w;
+      b200::PrepareWorkspace(&w, g, sizeof(T), ctx.GetPlace(), stream);
+      b200::StatusWord status(ctx.GetPlace(), stream);
+      B200EMB_CHECK(b200::Api<T>::sgd(param_out->data<T>(), g.height, g.d, g.rows, static_cast<const T*>(g.value), g.n,
+                                      learning_rate->data<T>(), w.ptr, w.bytes, w.flags, status.get(), stream));
+      b200::SideTable::Instance().Release(device, g.plan);
+      status.Enforce("sgd");
     } else {
       PADDLE_THROW("Unsupported Variable Type of Grad");
     }

@@ -3,6 +3,7 @@
 // LoDTensor output: dense inputs are added element-wise, SelectedRows inputs are accumulated with
 // the duplicate-merging kernel (sum_op.h:40-70 / SelectedRowsAddToTensor).
 #include <memory>
+#include <type_traits>
 #include <vector>
 #include "b200_op_common.h"
 #include "paddle/fluid/framework/lod_tensor.h"
@@ -31,6 +32,7 @@ class SumB200Kernel : public framework::OpKernel<T> {
     const bool in_place = out_var == in_vars[0];
     auto stream = context.cuda_device_context().stream();
     const auto place = context.GetPlace();
+    const int device = boost::get<platform::CUDAPlace>(place).device;
 
     if (out_var->IsType<LoDTensor>()) {
       auto* out = context.Output<LoDTensor>("Out");
@@ -44,16 +46,19 @@ class SumB200Kernel : public framework::OpKernel<T> {
           const int grid = static_cast<int>(std::min<int64_t>((numel + 255) / 256, 148 * 8));
           AddInto<T><<<grid, 256, 0, stream>>>(in_t.data<T>(), numel, out_data);
         } else if (in_vars[i]->IsType<SelectedRows>()) {
-          auto& in_t = in_vars[i]->Get<SelectedRows>();
-          const int64_t n = static_cast<int64_t>(in_t.rows().size());
-          if (n == 0) continue;
-          const int64_t height = in_t.height(), d = in_t.value().numel() / n;
-          PADDLE_ENFORCE_EQ(height, out->dims()[0]);
-          framework::Tensor ws;
-          size_t ws_bytes = 0;
-          void* wsp = b200::Workspace(&ws, n, d, sizeof(T), place, &ws_bytes);
-          B200EMB_CHECK(b200::Api<T>::add_to_tensor(in_t.rows().CUDAData(place), in_t.value().data<T>(), n, d, height,
-                                                    out_data, wsp, ws_bytes, b200::Flags(), nullptr, stream));
+          if constexpr (std::is_floating_point<T>::value) {
+            auto& in_t = in_vars[i]->Get<SelectedRows>();
+            const b200::SparseGradView g = b200::ViewSparseGrad<T>(device, place, &in_t);
+            if (g.n == 0) continue;
+            PADDLE_ENFORCE_EQ(g.height, out->dims()[0]);
+            b200::UpdateWorkspace w;
+            b200::PrepareWorkspace(&w, g, sizeof(T), place, stream);
+            B200EMB_CHECK(b200::Api<T>::add_to_tensor(g.rows, static_cast<const T*>(g.value), g.n, g.d, g.height,
+                                                      out_data, w.ptr, w.bytes, w.flags, nullptr, stream));
+            b200::SideTable::Instance().Release(device, g.plan);
+          } else {
+            PADDLE_THROW("sum: SelectedRows inputs need a float or double kernel");
+          }
         } else {
           PADDLE_THROW("Variable type must be LoDTensor/SelectedRows.");
         }
@@ -63,27 +68,30 @@ class SumB200Kernel : public framework::OpKernel<T> {
       std::unique_ptr<SelectedRows> in0;
       if (in_place) {
         auto& src = in_vars[0]->Get<SelectedRows>();
-        const int64_t n0 = static_cast<int64_t>(src.rows().size());
+        const b200::SparseGradView g0 = b200::ViewSparseGrad<T>(device, place, &src);   // fused mode: device pointers
+        const int64_t n0 = g0.n;
         in0.reset(new SelectedRows(std::vector<int64_t>(), src.height()));
         in0->mutable_rows()->resize(static_cast<size_t>(n0));
         in0->mutable_value()->Resize(src.value().dims());
         if (n0 > 0) {
           T* v = in0->mutable_value()->mutable_data<T>(place);
           int64_t* r = in0->mutable_rows()->CUDAMutableData(place);
-          B200EMB_CHECK(b200emb_selected_rows_add_to(src.rows().CUDAData(place), src.value().data<T>(), n0,
-                                                     src.value().numel() / n0, sizeof(T), r, v, 0, stream));
+          B200EMB_CHECK(b200emb_selected_rows_add_to(g0.rows, g0.value, n0, g0.d, sizeof(T), r, v, 0, stream));
         }
+        b200::SideTable::Instance().Release(device, g0.plan);
       }
       auto get = [&](int i) -> const SelectedRows& {
         return (i == 0 && in0) ? *in0 : in_vars[i]->Get<SelectedRows>();
       };
+      // fused mode: the inputs' rows / values are read from the device pointers the producers recorded
+      std::vector<b200::SparseGradView> views(N);
+      for (int i = 0; i < N; ++i) views[i] = b200::ViewSparseGrad<T>(device, place, &get(i));
       auto* out = context.Output<SelectedRows>("Out");
       int64_t total = 0;
       std::vector<int64_t> in_dim;
       for (int i = 0; i < N; ++i) {
-        const SelectedRows& s = get(i);
-        total += static_cast<int64_t>(s.rows().size());
-        if (in_dim.empty() && s.rows().size() > 0) in_dim = framework::vectorize(s.value().dims());
+        total += views[i].n;
+        if (in_dim.empty() && views[i].n > 0) in_dim = framework::vectorize(get(i).value().dims());
       }
       if (in_dim.empty()) in_dim = framework::vectorize(get(N - 1).value().dims());   // all inputs empty
       else in_dim[0] = total;
@@ -93,22 +101,39 @@ class SumB200Kernel : public framework::OpKernel<T> {
       out_value->Resize(framework::make_ddim(in_dim));
       T* out_data = out_value->mutable_data<T>(place);
       if (total == 0) return;
-      int64_t* out_rows = out->mutable_rows()->CUDAMutableData(place);
+      const bool fused_out = b200::SideTable::Instance().fused();
+      // fused mode keeps the concatenated rows in a device tensor of its own; rows() keeps only its size
+      int64_t* out_rows = nullptr;
+      std::shared_ptr<framework::Tensor> rows_dev;
+      if (fused_out) {
+        rows_dev = std::make_shared<framework::Tensor>();
+        out_rows = rows_dev->mutable_data<int64_t>(framework::make_ddim({total}), place);
+      } else {
+        out_rows = out->mutable_rows()->CUDAMutableData(place);
+      }
       const int64_t d = out_value->numel() / total;
       // Runtime InferShape (SumOp::InferShape, sum_op.cc:33-64, through RuntimeInferShapeContext::SetDim,
       // operator.cc:608-622) gives Out the complete dims of the inputs, i.e. their height, before the kernel
       // runs; the mini runner has no InferShape pass, so the same assignment happens here.
       for (int i = 0; i < N; ++i)
-        if (get(i).rows().size() > 0) { out->set_height(get(i).height()); break; }
+        if (views[i].n > 0) { out->set_height(views[i].height); break; }
       int64_t offset = 0;
       for (int i = 0; i < N; ++i) {
-        const SelectedRows& s = get(i);
-        const int64_t n = static_cast<int64_t>(s.rows().size());
-        if (n == 0) continue;
-        PADDLE_ENFORCE_EQ(out->height(), s.height());
-        B200EMB_CHECK(b200emb_selected_rows_add_to(s.rows().CUDAData(place), s.value().data<T>(), n, d, sizeof(T),
-                                                   out_rows, out_data, offset, stream));
-        offset += n;
+        const b200::SparseGradView& g = views[i];
+        if (g.n == 0) continue;
+        PADDLE_ENFORCE_EQ(out->height(), g.height);
+        B200EMB_CHECK(b200emb_selected_rows_add_to(g.rows, g.value, g.n, d, sizeof(T), out_rows, out_data, offset,
+                                                   stream));
+        b200::SideTable::Instance().Release(device, g.plan);   // a plan of one input is of no use to the concatenation
+        offset += g.n;
+      }
+      if (fused_out) {
+        b200::SparseGradRecord rec;
+        rec.ids = out_rows;
+        rec.value = out_data;
+        rec.n = total; rec.d = d; rec.height = out->height();
+        rec.keep = rows_dev;
+        b200::SideTable::Instance().Bind(device, out, rec);
       }
     } else {
       PADDLE_THROW("Unexpected branch, output variable type is %s", out_var->Type().name());
@@ -120,4 +145,6 @@ class SumB200Kernel : public framework::OpKernel<T> {
 }  // namespace paddle
 
 namespace ops = paddle::operators;
-REGISTER_OP_CUDA_KERNEL(sum, ops::SumB200Kernel<float>, ops::SumB200Kernel<double>);
+// the reference registers four element types (operators/sum_op.cu:16-20)
+REGISTER_OP_CUDA_KERNEL(sum, ops::SumB200Kernel<float>, ops::SumB200Kernel<double>, ops::SumB200Kernel<int>,
+                        ops::SumB200Kernel<int64_t>);

@@ -204,5 +204,11 @@ class Operator:
                                ";".join(attrs).encode(), place.device))
 
 
+def set_fused(on):
+    """FLAGS_b200emb_fused: the sparse gradient stays on the device between lookup_table_grad, sum and the
+    optimizer op (no rows() round trip, no copies) and lookup_table starts the sort plan early."""
+    lib().fl_set_fused(1 if on else 0)
+
+
 def registered_kernels(op_type):
     return int(lib().fl_num_registered_kernels(op_type.encode()))

@@ -23,8 +23,9 @@ def core(pkg):
 
 
 def test_kernels_are_registered(core):
-    for op in ("lookup_table", "lookup_table_grad", "sum", "sgd", "adam", "adagrad"):
+    for op in ("lookup_table", "lookup_table_grad", "sgd", "adam", "adagrad"):
         assert core.registered_kernels(op) == 2        # float + double, CUDAPlace
+    assert core.registered_kernels("sum") == 4         # + int, int64 (operators/sum_op.cu:16-20)
 
 
 def test_no_cpu_kernel(core):
@@ -92,6 +93,111 @@ def test_lookup_table_grad_sparse_then_sum_then_sgd_word2vec_shape(core):
     assert np.abs(got - truth).max() < 1e-7
     untouched = np.setdiff1d(np.arange(V), all_ids)
     assert np.array_equal(got[untouched], table[untouched])
+
+
+def _embedding_step(core, fused, lookups, V, D, B, optimizer, seed=0):
+    """lookup_table x lookups -> lookup_table_grad x lookups -> [sum] -> sgd|adam through Operator.run; returns
+    (forward outputs, updated table)."""
+    place = core.CUDAPlace(0)
+    rng = np.random.default_rng(seed)
+    table = (rng.random((V, D)) * 0.1 - 0.05).astype(np.float32)
+    ids = [(rng.zipf(1.3, (B, 1)) % V).astype(np.int64) for _ in range(lookups)]
+    douts = [(rng.standard_normal((B, D)) * 0.01).astype(np.float32) for _ in range(lookups)]
+    core.set_fused(fused)
+    try:
+        scope = core.Scope()
+        scope.var("w").get_tensor().set(table, place)
+        scope.var("lr").get_tensor().set(np.array([0.01], np.float32), place)
+        outs = []
+        for k in range(lookups):
+            scope.var("ids%d" % k).get_tensor().set(ids[k], place)
+            core.Operator("lookup_table", W="w", Ids="ids%d" % k, Out="emb%d" % k, is_sparse=True).run(scope, place)
+            outs.append(np.array(scope.var("emb%d" % k).get_tensor()))
+        for k in range(lookups):
+            scope.var("emb%d@GRAD" % k).get_tensor().set(douts[k], place)
+            scope.var("g%d" % k).get_selected_rows()
+            core.Operator("lookup_table_grad", W="w", Ids="ids%d" % k, is_sparse=True,
+                          **{"Out@GRAD": "emb%d@GRAD" % k, "W@GRAD": "g%d" % k}).run(scope, place)
+        grad = "g0"
+        if lookups > 1:
+            scope.var("w@GRAD").get_selected_rows().set_height(V)
+            core.Operator("sum", X=["g%d" % k for k in range(lookups)], Out="w@GRAD").run(scope, place)
+            grad = "w@GRAD"
+        if optimizer == "sgd":
+            core.Operator("sgd", Param="w", Grad=grad, ParamOut="w", LearningRate="lr").run(scope, place)
+        else:
+            for name, val in (("m1", np.zeros((V, D), np.float32)), ("m2", np.zeros((V, D), np.float32)),
+                              ("b1p", np.array([0.9], np.float32)), ("b2p", np.array([0.999], np.float32))):
+                scope.var(name).get_tensor().set(val, place)
+            core.Operator("adam", Param="w", Grad=grad, LearningRate="lr", Moment1="m1", Moment2="m2", Beta1Pow="b1p",
+                          Beta2Pow="b2p", ParamOut="w", Moment1Out="m1", Moment2Out="m2").run(scope, place)
+        return outs, np.array(scope.var("w").get_tensor()), table, ids, douts
+    finally:
+        core.set_fused(False)
+
+
+@pytest.mark.parametrize("lookups,optimizer,B", [(1, "sgd", 40000), (4, "sgd", 3000), (1, "adam", 20000)])
+def test_fused_mode_equals_materialised_mode(core, lookups, optimizer, B):
+    """FLAGS_b200emb_fused (b200_side_table.h): the gradient stays on the device — no rows() round trip, no
+    copies, sort plan started by the forward op — and the step gives the same bits as the materialised mode
+    (same plan, same reduction tree), which in turn is checked against the oracle."""
+    V, D = 50021, 64
+    outs_a, w_a, table, ids, douts = _embedding_step(core, False, lookups, V, D, B, optimizer)
+    outs_b, w_b, _, _, _ = _embedding_step(core, True, lookups, V, D, B, optimizer)
+    for a, b in zip(outs_a, outs_b):
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    assert np.array_equal(w_a.view(np.uint32), w_b.view(np.uint32))
+    if optimizer == "sgd":
+        all_ids = np.concatenate([i.flatten() for i in ids])
+        all_g = np.concatenate(douts)
+        rows, merged = oracle.merge_add(all_ids, all_g, truth=True)
+        _, l1 = oracle.merge_add(all_ids, np.abs(all_g), truth=True)
+        truth = table.astype(np.float64)
+        truth[rows] -= 0.01 * merged
+        bound = 1e-6 * np.abs(table).astype(np.float64)
+        bound[rows] += 1e-6 * 0.01 * l1
+        assert (np.abs(w_b - truth) <= bound + 1e-30).all()
+
+
+def test_lookup_table_grad_dense_branch(core):
+    """is_sparse=False (lookup_table_op.h:135-157): W@GRAD is a dense [V, D] tensor, zero except the looked-up
+    rows, duplicates accumulated."""
+    place = core.CUDAPlace(0)
+    rng = np.random.default_rng(3)
+    V, D, B = 301, 24, 500
+    table = rng.random((V, D)).astype(np.float32)
+    ids = rng.integers(0, V // 3, (B, 1)).astype(np.int64)
+    dout = (rng.standard_normal((B, D)) * 0.1).astype(np.float32)
+    scope = core.Scope()
+    scope.var("W").get_tensor().set(table, place)
+    scope.var("Ids").get_tensor().set(ids, place)
+    scope.var("Out@GRAD").get_tensor().set(dout, place)
+    core.Operator("lookup_table_grad", W="W", Ids="Ids", is_sparse=False,
+                  **{"Out@GRAD": "Out@GRAD", "W@GRAD": "W@GRAD"}).run(scope, place)
+    got = np.array(scope.var("W@GRAD").get_tensor())
+    want = oracle.lookup_table_grad_dense(ids.flatten(), dout, V)
+    assert got.shape == (V, D)
+    truth = np.zeros((V, D))
+    np.add.at(truth, ids.flatten(), dout.astype(np.float64))
+    l1 = np.zeros((V, D))
+    np.add.at(l1, ids.flatten(), np.abs(dout).astype(np.float64))
+    assert (np.abs(got - truth) <= 1e-6 * l1 + 1e-30).all()
+    assert np.allclose(got, want, rtol=1e-5, atol=1e-7)
+    assert not got[V // 3:].any()
+
+
+@pytest.mark.parametrize("dtype", [np.int32, np.int64])
+def test_sum_op_integer_tensors(core, dtype):
+    """sum is registered for int and int64 too (operators/sum_op.cu:16-20): dense LoDTensor inputs."""
+    place = core.CUDAPlace(0)
+    rng = np.random.default_rng(4)
+    xs = [rng.integers(-1000, 1000, (37, 5)).astype(dtype) for _ in range(3)]
+    scope = core.Scope()
+    for k, x in enumerate(xs):
+        scope.var("x%d" % k).get_tensor().set(x, place)
+    scope.var("out").get_tensor().set(np.zeros((37, 5), dtype), place)
+    core.Operator("sum", X=["x0", "x1", "x2"], Out="out").run(scope, place)
+    assert np.array_equal(np.array(scope.var("out").get_tensor()), xs[0] + xs[1] + xs[2])
 
 
 def test_sparse_sgd_op(core):
