@@ -31,6 +31,10 @@ class Place {
   const CUDAPlace& gpu() const { return gpu_; }
   bool operator==(const Place& o) const { return is_gpu_ == o.is_gpu_ && (!is_gpu_ || gpu_ == o.gpu_); }
   bool operator!=(const Place& o) const { return !(*this == o); }
+  bool operator<(const Place& o) const {   // CPU before GPUs, GPUs by device id (the variant's ordering)
+    if (is_gpu_ != o.is_gpu_) return !is_gpu_;
+    return is_gpu_ && gpu_.device < o.gpu_.device;
+  }
 
  private:
   bool is_gpu_;

@@ -144,10 +144,12 @@ __device__ __forceinline__ void signal_peers(unsigned long long* const* flag_dst
                                              const int64_t* starts, const unsigned long long* epoch,
                                              unsigned int* done_ctr, int world) {
   if (flag_dst == nullptr) return;
-  __threadfence_system();            // this thread's stores to peer memory are performed system-wide
-  __syncthreads();
+  __syncthreads();                   // every thread's stores to peer memory precede the barrier ...
   __shared__ bool s_last_cta;
-  if (threadIdx.x == 0) s_last_cta = atomicAdd(done_ctr, 1u) == gridDim.x - 1;
+  if (threadIdx.x == 0) {
+    __threadfence_system();          // ... so ONE cumulative fence per CTA performs them system-wide (the grid-sync
+    s_last_cta = atomicAdd(done_ctr, 1u) == gridDim.x - 1;   // idiom) before the CTA counts itself in
+  }
   __syncthreads();
   if (!s_last_cta) return;
   __threadfence_system();            // the other CTAs' fenced stores, observed through the counter

@@ -108,8 +108,8 @@ struct WaitSpec {
   int32_t* status = nullptr;                   // B200EMB_STATUS_BARRIER_TIMEOUT after ~20 s
 };
 
-// Optional publication at the end of a producer kernel of the sharded path.  Every thread fences its stores to
-// the other GPUs (fence.sys) before its CTA counts itself in; the last CTA to finish writes, per destination
+// Optional publication at the end of a producer kernel of the sharded path.  Every CTA fences its stores to
+// the other GPUs (barrier, then one cumulative fence.sys) before it counts itself in; the last CTA to finish writes, per destination
 // rank r, the payload {starts[r], starts[r+1]-starts[r]} (if payload_dst) and then the flag = *epoch
 // (st.release.sys) — data and flag leave from the same kernel, ordered by the fences of the threads that
 // wrote the data.  flag_dst == nullptr: nothing is published.

@@ -139,10 +139,12 @@ k_send_ids(const int64_t* __restrict__ local, const int64_t* __restrict__ bounds
     if (k < cap_src) T.ids_in[g][k] = local[u];
     else atomicOr(status, B200EMB_STATUS_SHARD_OVERFLOW);
   }
-  __threadfence_system();
   __syncthreads();
   __shared__ bool s_last;
-  if (threadIdx.x == 0) s_last = atomicAdd(done_ctr, 1u) == gridDim.x - 1;
+  if (threadIdx.x == 0) {
+    __threadfence_system();          // one cumulative fence per CTA, after the barrier that collects its threads' stores
+    s_last = atomicAdd(done_ctr, 1u) == gridDim.x - 1;
+  }
   __syncthreads();
   if (!s_last) return;
   __threadfence_system();

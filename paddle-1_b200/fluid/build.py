@@ -9,7 +9,7 @@ PKG = os.path.dirname(HERE)
 ROOT = os.path.dirname(PKG)
 OUT = os.path.join(PKG, "libb200emb_fluid.so")
 SOURCES = ["lookup_table_op.cu", "sum_op.cu", "sgd_op.cu", "adam_op.cu", "adagrad_op.cu", "split_ids_op.cu",
-           "split_selected_rows_op.cu", "runner.cu"]
+           "split_selected_rows_op.cu", "sparse_all_to_all_op_handle.cu", "runner.cu"]
 
 
 def _newer(target, deps):
@@ -21,7 +21,7 @@ def _newer(target, deps):
 
 def build(force=False, verbose=False):
     srcs = [os.path.join(HERE, s) for s in SOURCES]
-    deps = list(srcs) + [os.path.join(HERE, "b200_op_common.h"), os.path.join(PKG, "libb200emb.so")]
+    deps = list(srcs) + [os.path.join(HERE, h) for h in ("b200_op_common.h", "b200_side_table.h", "sparse_all_to_all_op_handle.h")] + [os.path.join(PKG, "libb200emb.so")]
     for base, _, files in os.walk(os.path.join(PKG, "compat")):
         deps += [os.path.join(base, f) for f in files]
     if not (force or _newer(OUT, deps)):

@@ -14,6 +14,7 @@
 #include "paddle/fluid/framework/op_registry.h"
 #include "paddle/fluid/framework/selected_rows.h"
 #include "b200_side_table.h"
+#include "sparse_all_to_all_op_handle.h"
 
 namespace fw = paddle::framework;
 namespace pf = paddle::platform;
@@ -244,6 +245,120 @@ int fl_set_fused(int on) {
 int fl_num_registered_kernels(const char* type) {
   auto it = fw::AllOpKernels().find(type);
   return it == fw::AllOpKernels().end() ? 0 : static_cast<int>(it->second.size());
+}
+
+}  // extern "C"
+
+// ---- a stand-in for the part of ParallelExecutor the sharded-table op handles need: N local scopes, one
+// device context per GPU (ranks that share a GPU share its stream), the handles wired to per-device variables
+namespace {
+namespace fd = paddle::framework::details;
+struct ParallelSession {
+  std::vector<std::unique_ptr<Session>> locals;
+  std::vector<pf::Place> places;
+  std::map<int, std::unique_ptr<pf::CUDADeviceContext>> ctxs;
+  std::unique_ptr<fd::ShardedTableContext> table;
+  std::vector<std::unique_ptr<fd::VarHandle>> handles;   // kept alive for the op handles of the last run
+  std::vector<fw::Scope*> scopes() {
+    std::vector<fw::Scope*> v;
+    for (auto& l : locals) v.push_back(&l->scope);
+    return v;
+  }
+  void wire(fd::OpHandleBase* op) {
+    for (size_t i = 0; i < places.size(); ++i)
+      op->SetDeviceContext(places[i], ctxs[boost::get<pf::CUDAPlace>(places[i]).device].get());
+  }
+  fd::VarHandle* var(size_t scope_idx, const char* name) {
+    handles.emplace_back(new fd::VarHandle(0, scope_idx, name, places[scope_idx]));
+    return handles.back().get();
+  }
+};
+}  // namespace
+
+extern "C" {
+
+void* fl_pe_new(int n, const int* devices) {
+  auto* pe = new ParallelSession();
+  for (int i = 0; i < n; ++i) {
+    pe->locals.emplace_back(new Session());
+    pe->places.push_back(pf::CUDAPlace(devices[i]));
+    if (!pe->ctxs.count(devices[i])) pe->ctxs[devices[i]].reset(new pf::CUDADeviceContext(pf::CUDAPlace(devices[i])));
+  }
+  return pe;
+}
+void fl_pe_free(void* p) { delete static_cast<ParallelSession*>(p); }
+void* fl_pe_scope(void* p, int i) { return static_cast<ParallelSession*>(p)->locals[i].get(); }
+
+// the pass's set-up for one embedding parameter: `param` (and moments) in local scope d hold device d's shard
+int fl_pe_shard_table(void* p, const char* param, const char* m1, const char* m2, int64_t height, int64_t d,
+                      int optimizer, int64_t max_ids, int64_t max_recv) {
+  FL_TRY
+  auto* pe = static_cast<ParallelSession*>(p);
+  std::vector<float*> shards, mom1, mom2;
+  for (size_t i = 0; i < pe->locals.size(); ++i) {
+    auto get = [&](const char* name) {
+      auto* v = pe->locals[i]->scope.FindVar(name);
+      PADDLE_ENFORCE_NOT_NULL(v, "variable %s not found in local scope %d", name, static_cast<int>(i));
+      return v->GetMutable<fw::LoDTensor>()->data<float>();
+    };
+    shards.push_back(get(param));
+    if (optimizer == B200EMB_SHARD_ADAM) { mom1.push_back(get(m1)); mom2.push_back(get(m2)); }
+  }
+  pe->table.reset(new fd::ShardedTableContext(pe->places, height, d, optimizer, shards, mom1, mom2, max_ids, max_recv));
+  return 0;
+  FL_CATCH(-1)
+}
+
+int fl_pe_sharded_lookup(void* p, const char* ids, const char* out) {
+  FL_TRY
+  auto* pe = static_cast<ParallelSession*>(p);
+  PADDLE_ENFORCE_NOT_NULL(pe->table.get(), "fl_pe_shard_table first");
+  pe->handles.clear();
+  fd::ShardedLookupOpHandle op(pe->scopes(), pe->table.get());
+  pe->wire(&op);
+  for (size_t i = 0; i < pe->places.size(); ++i) op.AddInput(pe->var(i, ids));
+  for (size_t i = 0; i < pe->places.size(); ++i) op.AddOutput(pe->var(i, out));
+  op.Run(true);
+  return 0;
+  FL_CATCH(-1)
+}
+
+int fl_pe_sparse_all_to_all(void* p, const char* grad, const char* lr, const char* b1p, const char* b2p, float beta1,
+                            float beta2, float epsilon) {
+  FL_TRY
+  auto* pe = static_cast<ParallelSession*>(p);
+  PADDLE_ENFORCE_NOT_NULL(pe->table.get(), "fl_pe_shard_table first");
+  pe->handles.clear();
+  fd::SparseAllToAllOpHandle op(pe->scopes(), pe->table.get(), beta1, beta2, epsilon);
+  pe->wire(&op);
+  const char* names[4] = {grad, lr, b1p, b2p};
+  const int groups = (b1p && b1p[0]) ? 4 : 2;
+  for (int k = 0; k < groups; ++k)
+    for (size_t i = 0; i < pe->places.size(); ++i) op.AddInput(pe->var(i, names[k]));
+  op.Run(true);
+  return 0;
+  FL_CATCH(-1)
+}
+
+// ParallelExecutor's end-of-run sync (every device context) + the engines' status words
+int fl_pe_sync(void* p) {
+  FL_TRY
+  auto* pe = static_cast<ParallelSession*>(p);
+  for (auto& kv : pe->ctxs) {
+    PADDLE_ENFORCE(cudaSetDevice(kv.first) == cudaSuccess);
+    kv.second->Wait();
+    cudaError_t e = cudaGetLastError();
+    PADDLE_ENFORCE(e == cudaSuccess, "CUDA error: %s", cudaGetErrorString(e));
+  }
+  int bits = 0;
+  if (pe->table)
+    for (int d = 0; d < pe->table->world(); ++d) {
+      int32_t st = 0;
+      PADDLE_ENFORCE(cudaMemcpy(&st, b200emb_shard_status_ptr(pe->table->engine(d)), sizeof(st), cudaMemcpyDeviceToHost) == cudaSuccess);
+      bits |= st;
+    }
+  return bits;
+  FL_CATCH(-1)
 }
 
 }  // extern "C"

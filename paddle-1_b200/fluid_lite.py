@@ -58,6 +58,8 @@ def lib():
         _LIB = ctypes.CDLL(path)
         _LIB.fl_last_error.restype = ctypes.c_char_p
         _LIB.fl_session_new.restype = ctypes.c_void_p
+        _LIB.fl_pe_new.restype = ctypes.c_void_p
+        _LIB.fl_pe_scope.restype = ctypes.c_void_p
         _LIB.fl_sr_height.restype = ctypes.c_int64
         _LIB.fl_sr_num_rows.restype = ctypes.c_int64
     return _LIB
@@ -151,12 +153,14 @@ class Variable:
 
 
 class Scope:
-    def __init__(self):
-        self._h = ctypes.c_void_p(lib().fl_session_new())
+    def __init__(self, handle=None):
+        self._owned = handle is None
+        self._h = ctypes.c_void_p(lib().fl_session_new() if handle is None else handle)
 
     def __del__(self):
         try:
-            lib().fl_session_free(self._h)
+            if self._owned:
+                lib().fl_session_free(self._h)
         except Exception:
             pass
 
@@ -212,3 +216,40 @@ def set_fused(on):
 
 def registered_kernels(op_type):
     return int(lib().fl_num_registered_kernels(op_type.encode()))
+
+
+class ShardedParallelSession:
+    """The slice of ParallelExecutor the sharded-table op handles need (fluid/sparse_all_to_all_op_handle.h):
+    one local scope per device (a device id may repeat: several ranks on one GPU, like the fake places of the
+    reference's op-handle tests), the pass's set-up for one embedding parameter, and one Run of each handle."""
+
+    SGD, ADAM = 0, 1
+
+    def __init__(self, devices):
+        arr = (ctypes.c_int * len(devices))(*devices)
+        self._h = ctypes.c_void_p(lib().fl_pe_new(len(devices), arr))
+        self.devices = list(devices)
+        self.scopes = [Scope(lib().fl_pe_scope(self._h, i)) for i in range(len(devices))]
+
+    def __del__(self):
+        try:
+            lib().fl_pe_free(self._h)
+        except Exception:
+            pass
+
+    def shard_table(self, param, height, d, max_ids, max_recv, optimizer="sgd", moment1="", moment2=""):
+        _check(lib().fl_pe_shard_table(self._h, param.encode(), moment1.encode(), moment2.encode(),
+                                       ctypes.c_int64(height), ctypes.c_int64(d),
+                                       self.ADAM if optimizer == "adam" else self.SGD,
+                                       ctypes.c_int64(max_ids), ctypes.c_int64(max_recv)))
+
+    def sharded_lookup(self, ids, out):
+        _check(lib().fl_pe_sharded_lookup(self._h, ids.encode(), out.encode()))
+
+    def sparse_all_to_all(self, grad, lr, beta1_pow="", beta2_pow="", beta1=0.9, beta2=0.999, epsilon=1e-8):
+        _check(lib().fl_pe_sparse_all_to_all(self._h, grad.encode(), lr.encode(), beta1_pow.encode(), beta2_pow.encode(),
+                                             ctypes.c_float(beta1), ctypes.c_float(beta2), ctypes.c_float(epsilon)))
+
+    def sync(self):
+        """Waits for every device; returns the OR of the engines' status words."""
+        return _check(lib().fl_pe_sync(self._h))

@@ -493,3 +493,93 @@ def test_extract_rows_op(core):
     core.Operator("extract_rows", X="X", Out="Out").run(scope, place)
     result = np.array(scope.var("Out").get_tensor())
     assert result.shape == (4, 1) and [e[0] for e in result] == rows
+
+
+# ------------------------------------------------------------------ SparseAllToAllOpHandle
+def _run_sharded_handles(core, devices, V, D, ids_per_dev, grads_per_dev, table, fused, steps=1, lr=0.5):
+    """ShardedLookupOpHandle -> lookup_table_grad per device -> SparseAllToAllOpHandle, `steps` times."""
+    G = len(devices)
+    hs = (V + G - 1) // G
+    pe = core.ShardedParallelSession(devices)
+    for d in range(G):
+        shard = np.zeros((hs, D), np.float32)
+        rows = np.arange(d, V, G)
+        shard[:len(rows)] = table[rows]
+        sc, place = pe.scopes[d], core.CUDAPlace(devices[d])
+        sc.var("emb_w").get_tensor().set(shard, place)
+        sc.var("lr").get_tensor().set(np.array([lr], np.float32), place)
+    n_max = max(len(i) for i in ids_per_dev)
+    pe.shard_table("emb_w", V, D, n_max, 2 * n_max * G)
+    core.set_fused(fused)
+    outs = []
+    try:
+        for _ in range(steps):
+            for d in range(G):
+                pe.scopes[d].var("ids").get_tensor().set(ids_per_dev[d].reshape(-1, 1), core.CUDAPlace(devices[d]))
+            pe.sharded_lookup("ids", "emb")
+            assert pe.sync() == 0
+            outs = [np.array(pe.scopes[d].var("emb").get_tensor()) for d in range(G)]
+            for d in range(G):        # the per-device gradient op of the replica, as ParallelExecutor would run it
+                sc, place = pe.scopes[d], core.CUDAPlace(devices[d])
+                sc.var("emb@GRAD").get_tensor().set(grads_per_dev[d], place)
+                sc.var("emb_w@GRAD").get_selected_rows()
+                core.Operator("lookup_table_grad", W="emb_w", Ids="ids", is_sparse=True,
+                              **{"Out@GRAD": "emb@GRAD", "W@GRAD": "emb_w@GRAD"}).run(sc, place)
+            pe.sparse_all_to_all("emb_w@GRAD", "lr")
+            assert pe.sync() == 0
+    finally:
+        core.set_fused(False)
+    shards = [np.array(pe.scopes[d].var("emb_w").get_tensor()) for d in range(G)]
+    full = np.stack(shards, axis=1).reshape(G * hs, D)[:V]
+    return outs, full
+
+
+@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("fused", [False, True], ids=["materialised", "fused"])
+def test_sparse_all_to_all_op_handle_reduce_test_case(core, world, fused):
+    """reduce_op_handle_test.cc:153-209 (TestReduceSelectedRows) re-expressed for the sharded result: every
+    device holds the SAME 20-row SelectedRows with duplicates, value[k] = k; where the reference checks the
+    gathered rows == the concatenation in device order, here the table rows must have received exactly that
+    concatenation: row r changes by lr * (sum over devices and occurrences of the value rows of r)."""
+    kDims = (20, 20)
+    V, D = kDims[0] * 2, kDims[1]
+    rows = np.array([0, 1, 2, 3, 3, 0, 14, 7, 3, 1, 2, 4, 6, 3, 1, 1, 1, 1, 3, 7], np.int64)
+    send = np.arange(kDims[0] * kDims[1], dtype=np.float32).reshape(kDims)
+    table = np.random.default_rng(1).random((V, D)).astype(np.float32)
+    devices = [0] * world if torch.cuda.device_count() < world else list(range(world))
+    outs, full = _run_sharded_handles(core, devices, V, D, [rows] * world, [send] * world, table, fused)
+    for o in outs:
+        assert np.array_equal(o, table[rows])                           # sharded lookup == lookup_table on the full table
+    want = table.copy()
+    cat_rows, cat_val = np.tile(rows, world), np.tile(send, (world, 1))  # gather-concat in device order
+    oracle.sgd_sparse(want, cat_rows, cat_val, np.array([0.5], np.float32))
+    truth = table.astype(np.float64)
+    r_, merged = oracle.merge_add(cat_rows, cat_val, truth=True)
+    truth[r_] -= 0.5 * merged
+    assert np.allclose(full, truth, rtol=1e-6, atol=1e-4)                # values up to 399 * lr * occurrences
+    assert np.allclose(full, want, rtol=1e-5, atol=1e-3)
+    untouched = np.setdiff1d(np.arange(V), rows)
+    assert np.array_equal(full[untouched], table[untouched])
+
+
+def test_sparse_all_to_all_op_handle_random_steps(core):
+    """Three consecutive steps of different per-device batches on 3 ranks (sharing GPU 0 when the box has fewer)."""
+    V, D, G = 5003, 32, 3
+    rng = np.random.default_rng(2)
+    table = (rng.random((V, D)) * 0.1 - 0.05).astype(np.float32)
+    ids = [(rng.zipf(1.2, 4000 + 100 * d) % V).astype(np.int64) for d in range(G)]
+    grads = [(rng.standard_normal((len(i), D)) * 0.01).astype(np.float32) for i in ids]
+    devices = [0] * G if torch.cuda.device_count() < G else list(range(G))
+    outs, full = _run_sharded_handles(core, devices, V, D, ids, grads, table, True, steps=3, lr=0.05)
+    truth = table.astype(np.float64)
+    bound = np.zeros_like(truth)
+    all_i, all_g = np.concatenate(ids), np.concatenate(grads)
+    r_, merged = oracle.merge_add(all_i, all_g, truth=True)
+    _, l1 = oracle.merge_add(all_i, np.abs(all_g), truth=True)
+    for _ in range(3):
+        last = truth.copy()
+        truth[r_] -= 0.05 * merged
+        bound[r_] += 1e-6 * 0.05 * l1
+    for d in range(G):      # the last lookup saw two updates
+        assert np.abs(outs[d] - last[ids[d]]).max() < 1e-6
+    assert (np.abs(full - truth) <= bound + 1e-6 * np.abs(truth) + 1e-30).all()
