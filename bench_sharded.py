@@ -181,9 +181,10 @@ def measure(pkg, tab, zipf, n, d, rank, world, dev, steps, warm, lr, want_e2e, u
 
 
 def phase_breakdown(eng, wl, lr, dev, steps):
-    names = ["prepare: sort plan + de-duplication (side stream, one batch ahead)", "send ids to owners",
-             "collect ids (waits for every source) + fork owner sort plan", "owner gather -> requesters, rows flags",
-             "expand to batch order (waits for every owner)", "local MergeAdd -> owners, gradient flags",
+    names = ["prepare: sort plan + de-duplication + ids to owners (side stream, one batch ahead)",
+             "owner gather -> requesters, rows flags (waits for every source's ids)",
+             "fork owner sort plan (side stream)", "expand to batch order (waits for every owner)",
+             "local MergeAdd -> owners, gradient flags",
              "owner fused update (waits for every source, joins owner sort plan)"]
     main = torch.cuda.current_stream(dev)
     side = torch.cuda.Stream(dev)
@@ -192,7 +193,7 @@ def phase_breakdown(eng, wl, lr, dev, steps):
     dist.barrier()
     for i in range(steps + 2):
         b = i % N_ROTATE
-        ev = [torch.cuda.Event(enable_timing=True) for _ in range(9)]
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(8)]
         side.wait_stream(main)
         with torch.cuda.stream(side):
             ev[0].record(side)
@@ -200,17 +201,17 @@ def phase_breakdown(eng, wl, lr, dev, steps):
             ev[1].record(side)
         main.wait_stream(side)
         ev[2].record(main)
-        for ph in range(4):
+        for ph in range(1, 4):
             eng.lookup(b, wl.out[b], phases=(ph, ph))
-            ev[3 + ph].record(main)
+            ev[2 + ph].record(main)
         for ph in range(2):
             eng.update(b, wl.dout[b], lr, phases=(ph, ph))
-            ev[7 + ph].record(main)
+            ev[6 + ph].record(main)
         evs.append(ev)
     torch.cuda.synchronize(dev)
     for ev in evs[2:]:
         acc[0] += ev[0].elapsed_time(ev[1])
-        for k in range(6):
+        for k in range(5):
             acc[1 + k] += ev[2 + k].elapsed_time(ev[3 + k])
     return {n_: round(a / steps * 1e3, 1) for n_, a in zip(names, acc)}
 
@@ -438,7 +439,9 @@ def run(args):
                     "nvlink_frac": nv / NVLINK_GBS}
         rf = roof(main)
         plan_k = capi.plan_kernel_count(n_main, tab.plan_h)
-        launches = (plan_k + capi.HEAD_SCAN_KERNELS + 2) + (2 + capi.plan_kernel_count(main["recv_rows"], tab.hs) + 3) + 3
+        # prepare: plan, head scan, inverse map, shard split, send ids | lookup: owner gather, owner plan, expand |
+        # update: local MergeAdd, owner update
+        launches = (plan_k + capi.HEAD_SCAN_KERNELS + 3) + (1 + capi.plan_kernel_count(main["recv_rows"], tab.hs) + 1) + 2
 
         def entry(r):
             e = {"ids_per_gpu_per_step": r["n"], "ms_per_step": r["ms_per_step"], "value": r["value"], "unit": UNIT,

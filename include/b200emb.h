@@ -278,17 +278,19 @@ int b200emb_exchange_maps(const int64_t* split_table, int world, int cols, int r
  *          torch.distributed, Fluid's gen_nccl_id RPC) and passes the world*64 bytes, in rank order, to connect().
  *          Ranks living in ONE process (ParallelExecutor: one thread per device) pass the block pointers
  *          (b200emb_shard_block) to connect_ptrs() instead, with peer access enabled by the caller.
- * prepare  the ids-only part of a step — sort plan, de-duplication, split points per owner — into one of 4
- *          slots; needs nothing but the ids, so a training loop can run it for batch i+1 on another stream
+ * prepare  the ids-only part of a step — sort plan, de-duplication, split points per owner, and the hand-over of
+ *          the unique row ids to their owners — into one of 4 slots; needs nothing but the ids, so a training
+ *          loop can run it for batch i+1 on another stream
  *          while batch i is in flight.  `ids` must stay valid until update() of that slot has run, and
  *          prepare(slot) overwrites the slot: order it (stream wait) after the update() that last used it.
  * lookup   out[k,:] = table[ids[k],:] for the slot's ids (lookup_table_op.h:36-84 over the sharded table).
  * update   sparse SGD / lazy Adam of the sharded table with the SelectedRows gradient {rows = the slot's ids,
  *          value = d_out} (sgd_op.h:47-81, adam_op.h:158-220,282-321): merged locally, merged rows sent to
  *          their owners, fused update there.  lr / beta*_pow are 1-element device tensors.
- * *_phases run a sub-range of the kernel sequence (lookup: 0 send ids, 1 collect + owner plan, 2 owner gather,
- *          3 expand; update: 0 merge + send, 1 owner update): a driver that hosts several ranks on ONE GPU
- *          issues phase k for every rank before phase k+1 (kernels that wait for each other must not share a GPU
+ * *_phases run a sub-range of the kernel sequence (lookup: 0 nothing — kept for callers of the first layout —,
+ *          1 owner gather into the requesters' buffers, 2 fork of the owner-side sort plan, 3 expand; update:
+ *          0 merge + send, 1 owner update): a driver that hosts several ranks on ONE GPU issues prepare() and
+ *          then phase k for every rank before phase k+1 (kernels that wait for each other must not share a GPU
  *          out of order); everybody else calls lookup()/update().
  * status_ptr  device int32 the kernels OR B200EMB_STATUS_* bits into; read it at your own sync points. */
 typedef struct b200emb_shard b200emb_shard_t;
@@ -397,6 +399,8 @@ int b200emb_sparse_adagrad_f64(double* param, double* moment, int64_t height, in
  *     may overlap on the GPU (other streams / threads) race — serialise them;
  *   - the first call on each device resolves the array's device address
  *     (cudaGetSymbolAddress); make that call before any stream capture;
+ *   - the current device must be the one that owns `param`, the other tensors and `stream` (the scratch used
+ *     is the current device's copy of the array); a `param` on another device is refused (B200EMB_E_INVALID);
  *   - B200EMB_PLAN_READY is rejected (B200EMB_E_INVALID); B200EMB_DETERMINISTIC is honoured. */
 #define B200EMB_NOALLOC_SCRATCH_BYTES (8 * 1024 * 1024)
 int b200emb_sparse_sgd_noalloc_f32(float* param, int64_t height, int64_t d, const int64_t* rows,

@@ -159,19 +159,46 @@ def dumps_lod_tensor(array, lod=()):
 
 
 # ------------------------------------------------------------------ row-sharded tables
-def save_sharded(path, shard, height, rank, world, group=None, slab_rows=1 << 20):
+def save_sharded(path, shard, height, rank, world, group=None, slab_rows=1 << 20, parallel=True):
     """Write the full [height, D] table (global row r lives at shard[r // world] of rank r % world) as one
-    reference-format LoDTensor file.  Every rank calls this; rank 0 writes.  `shard` is a torch tensor."""
+    reference-format LoDTensor file that fluid.io.load_persistables can read.  Every rank calls this.
+    parallel=True (ranks share a file system): rank 0 writes the header and sizes the file, then EVERY rank
+    stores its own rows (rank, rank + world, ...) through a shared memory map, slab by slab — no rank ever
+    holds more than one slab of someone else's data and nothing funnels through rank 0.
+    parallel=False: slabs are all-gathered and rank 0 writes them (works without a shared file system)."""
     import torch
     import torch.distributed as dist
     d = shard.shape[1]
     np_dtype = np.dtype(str(shard.dtype).replace("torch.", ""))
+    hs = shard.shape[0]
+    multi = world > 1 and dist.is_available() and dist.is_initialized()
+    if parallel:
+        offset = 0
+        if rank == 0:
+            with open(path, "wb") as f:
+                write_lod_header(f)
+                write_tensor_header(f, np_dtype, (height, d))
+                offset = f.tell()
+                f.truncate(offset + height * d * np_dtype.itemsize)
+        if multi:
+            box = [offset]
+            dist.broadcast_object_list(box, src=0, group=group)
+            offset = box[0]
+        full = np.memmap(path, dtype=np_dtype, mode="r+", offset=offset, shape=(height, d))
+        mine = full[rank::world]                      # this rank's rows, strided view of the file
+        for lo in range(0, mine.shape[0], slab_rows):
+            hi = min(mine.shape[0], lo + slab_rows)
+            mine[lo:hi] = shard[lo:hi].cpu().numpy()
+        full.flush()
+        del mine, full
+        if multi:
+            dist.barrier(group=group)
+        return
     f = None
     if rank == 0:
         f = open(path, "wb")
         write_lod_header(f)
         write_tensor_header(f, np_dtype, (height, d))
-    hs = shard.shape[0]
     written = 0
     for lo in range(0, hs, slab_rows):
         part = shard[lo:lo + slab_rows].contiguous()

@@ -108,11 +108,11 @@ struct WaitSpec {
   int32_t* status = nullptr;                   // B200EMB_STATUS_BARRIER_TIMEOUT after ~20 s
 };
 
-// Optional publication at the end of a producer kernel of the sharded path.  Every CTA fences its stores to
-// the other GPUs (barrier, then one cumulative fence.sys) before it counts itself in; the last CTA to finish writes, per destination
+// Optional publication at the end of a producer kernel of the sharded path.  Every CTA orders its stores to
+// the other GPUs before its arrival (barrier, then one cumulative gpu-scope fence); the last CTA to finish writes, per destination
 // rank r, the payload {starts[r], starts[r+1]-starts[r]} (if payload_dst) and then the flag = *epoch
-// (st.release.sys) — data and flag leave from the same kernel, ordered by the fences of the threads that
-// wrote the data.  flag_dst == nullptr: nothing is published.
+// (st.release.sys, the kernel's only system-scope fence, cumulative over all arrivals it observed) — data and
+// flag leave from the same kernel.  flag_dst == nullptr: nothing is published.
 struct SignalSpec {
   unsigned long long* const* flag_dst = nullptr;   // [world] device table: this rank's flag word on every rank
   int64_t* const* payload_dst = nullptr;           // [world] optional: two int64 per destination

@@ -67,6 +67,15 @@ extern "C" int b200emb_sparse_sgd_noalloc_f32(float* param, int64_t height, int6
   const size_t need = b200emb_workspace_bytes(n, d, sizeof(float));
   if (need == 0) return B200EMB_E_INVALID;
   if (need > static_cast<size_t>(B200EMB_NOALLOC_SCRATCH_BYTES)) return B200EMB_E_SCRATCH_LIMIT;
+  // the scratch used is the CURRENT device's: the table must live there too (a caller whose current device
+  // differs from the one owning its tensors would otherwise launch across devices)
+  cudaPointerAttributes attr;
+  int dev = -1;
+  if (cudaPointerGetAttributes(&attr, param) != cudaSuccess || cudaGetDevice(&dev) != cudaSuccess) {
+    cudaGetLastError();
+    return B200EMB_E_CUDA;
+  }
+  if (attr.type == cudaMemoryTypeDevice && attr.device != dev) return B200EMB_E_INVALID;
   void* scratch = nullptr;
   const int rc = scratch_for_current_device(&scratch);
   if (rc != B200EMB_OK) return rc;

@@ -158,16 +158,18 @@ __device__ __forceinline__ void load_state(const Params<T>& P, uint32_t key, int
 template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
 __device__ __forceinline__ void apply_state(const Params<T>& P, uint32_t key, uint32_t eref, int col0,
                                             int l, const T (&acc)[NV][Epv<T, VEC>::value],
-                                            RowState<T, OP, NV, Epv<T, VEC>::value>& st) {
+                                            RowState<T, OP, NV, Epv<T, VEC>::value>& st,
+                                            T* merge_dst_known = nullptr, bool merge_dst_is_known = false) {
   constexpr int EPV = Epv<T, VEC>::value;
   using A = Arith<T>;
   if (key >= P.height) return;  // out-of-range row: flagged by the sort plan, skipped here
-  const int64_t row = (OP == UpdateOp::kMergeAdd) ? static_cast<int64_t>(P.uidx[eref])
+  if (OP == UpdateOp::kMergeAdd && merge_dst_is_known && merge_dst_known == nullptr) return;   // refused by its owner
+  const int64_t row = (OP == UpdateOp::kMergeAdd) ? (merge_dst_is_known ? 0 : static_cast<int64_t>(P.uidx[eref]))
                                                   : static_cast<int64_t>(key);
   const int64_t base = row * P.d;
-  T* merge_dst = P.param + base;
+  T* merge_dst = merge_dst_is_known ? merge_dst_known : P.param + base;
   if constexpr (OP == UpdateOp::kMergeAdd) {
-    if (P.shards > 0) {
+    if (P.shards > 0 && !merge_dst_is_known) {
       int g = 0;
       while (g + 1 < P.shards && row >= P.shard_bounds[g + 1]) ++g;
       int64_t k = row - P.shard_bounds[g];
@@ -400,11 +402,13 @@ __device__ __forceinline__ void chunk_reduce_body(const uint32_t* __restrict__ s
   T* s_tail = s_head + GPC * COLS;                            // [GPC][COLS]
   uint32_t* s_key = reinterpret_cast<uint32_t*>(s_tail + GPC * COLS);  // [win]
   uint32_t* s_pos = s_key + win;                              // [win] original position | kCloses | kDirect
+  uint32_t* s_uidx = s_pos + win;                             // [win] kMergeAdd only: output row of each position
   __shared__ uint32_t s_flags[GPC];
   __shared__ int s_a, s_b, s_before, s_after, s_nfix, s_fix_c[2], s_fix_len[2];
 
   const int cta = blockIdx.x, num_ctas = gridDim.x;
   const int d = P.d;
+  const int64_t d_ = P.d;
   pdl_wait();
   pdl_launch_dependents();
   wait_for_flags(P.wait.flags, P.wait.epoch, P.wait.world, P.wait.status);
@@ -414,9 +418,47 @@ __device__ __forceinline__ void chunk_reduce_body(const uint32_t* __restrict__ s
   for (int i = w0 + tid; i < w1; i += kBlock) {
     s_key[i - w0] = skey[i];
     s_pos[i - w0] = perm[i];
+    if constexpr (OP == UpdateOp::kMergeAdd) s_uidx[i - w0] = P.uidx[i];
+  }
+  // kMergeAdd: where a merged row goes is a function of its output index and (with a scatter map) a few small
+  // per-destination tables: both are staged here so that closing a segment costs no dependent global load
+  constexpr int kSmemShards = 64;
+  __shared__ int64_t s_sb[OP == UpdateOp::kMergeAdd ? kSmemShards + 1 : 1];
+  __shared__ int64_t s_sm[OP == UpdateOp::kMergeAdd ? 2 * kSmemShards : 1];
+  __shared__ T* s_sd[OP == UpdateOp::kMergeAdd ? kSmemShards : 1];
+  const bool shard_tables = OP == UpdateOp::kMergeAdd && P.shards > 0 && P.shards <= kSmemShards;
+  if constexpr (OP == UpdateOp::kMergeAdd) {
+    if (shard_tables) {
+      if (tid <= P.shards) s_sb[tid] = P.shard_bounds[tid];
+      if (tid < P.shards) {
+        s_sd[tid] = P.shard_dst[tid];
+        s_sm[2 * tid] = P.shard_meta ? P.shard_meta[2 * tid] : 0;
+        s_sm[2 * tid + 1] = P.shard_meta ? P.shard_meta[2 * tid + 1] : (int64_t(1) << 62);
+      }
+    }
   }
   __syncthreads();
   const auto K = [&](int i) { return s_key[i - w0]; };          // w0 <= i < w1
+  // kMergeAdd: destination of the merged row that closes at sorted position idx (nullptr: its owner refused it)
+  const auto merge_dst_of = [&](int idx) -> T* {
+    const int64_t row = s_uidx[idx - w0];
+    if (P.shards == 0) return P.param + row * d_;
+    if (!shard_tables) {
+      int g = 0;
+      while (g + 1 < P.shards && row >= P.shard_bounds[g + 1]) ++g;
+      int64_t k = row - P.shard_bounds[g];
+      if (P.shard_meta) {
+        if (k >= P.shard_meta[2 * g + 1]) return nullptr;
+        k += P.shard_meta[2 * g];
+      }
+      return P.shard_dst[g] + k * d_;
+    }
+    int g = 0;
+    while (g + 1 < P.shards && row >= s_sb[g + 1]) ++g;
+    const int64_t k = row - s_sb[g];
+    if (k >= s_sm[2 * g + 1]) return nullptr;
+    return s_sd[g] + (k + s_sm[2 * g]) * d_;
+  };
   // adjusted boundary of nominal position p (the CTAs on both sides of it compute the same value)
   if (warp < 2) {
     const int p = warp == 0 ? nom_s : nom_e;
@@ -577,7 +619,11 @@ __device__ __forceinline__ void chunk_reduce_body(const uint32_t* __restrict__ s
             if (pw & kCloses) {   // the segment closes here
               if (pw & kDirect) {
                 const uint32_t key = K(idx);
-                if constexpr (RG::kStateInRing || NS == 0) {
+                if constexpr (OP == UpdateOp::kMergeAdd) {
+                  RowState<T, OP, NV, EPV> st;
+                  apply_state<T, OP, LPR, NV, VEC>(P, key, static_cast<uint32_t>(idx), col0, l, acc, st,
+                                                   merge_dst_of(idx), true);
+                } else if constexpr (RG::kStateInRing) {
                   RowState<T, OP, NV, EPV> st;
                   read_state(slot_addr, key, st);
                   apply_state<T, OP, LPR, NV, VEC>(P, key, static_cast<uint32_t>(idx), col0, l, acc, st);
@@ -659,6 +705,10 @@ __device__ __forceinline__ void chunk_reduce_body(const uint32_t* __restrict__ s
             }
         }
         apply_state<T, OP, LPR, NV, VEC>(P, tail_key, tail_eref, col0, l, sum, st);
+      } else if constexpr (OP == UpdateOp::kMergeAdd) {
+        RowState<T, OP, NV, EPV> st;
+        apply_state<T, OP, LPR, NV, VEC>(P, tail_key, tail_eref, col0, l, sum, st,
+                                         merge_dst_of(static_cast<int>(tail_eref)), true);
       } else {
         consume<T, OP, LPR, NV, VEC>(P, tail_key, tail_eref, col0, l, sum);
       }
@@ -886,7 +936,7 @@ cudaError_t launch_op(const SortedPlan& plan, const T* value, int64_t n, int64_t
       using RG = Ring<T, OP, NV, VEC>;
       const int batch = RG::batch_for(ring_target);
       const size_t smem = RG::bytes_for(batch) + sizeof(T) * 2 * GPC * COLS +
-                          sizeof(uint32_t) * 2 * (GPC * chunk + slack + 2);
+                          sizeof(uint32_t) * (OP == UpdateOp::kMergeAdd ? 3 : 2) * (GPC * chunk + slack + 2);
       const ChunkGeom G{ni, chunk, slack, batch};
       auto kern = k_chunk_reduce<T, OP, LPR, NV, VEC>;
       // opt in to > 48 KB of dynamic shared memory once per device (the attribute is per device)

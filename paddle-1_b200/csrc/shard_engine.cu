@@ -8,27 +8,30 @@
 //
 // One engine per rank (one GPU).  Every rank owns one peer-visible block (CUDA IPC between processes, plain
 // peer pointers inside one process) that the OTHER ranks' kernels store into over NVLink:
-//     header    int64 [8]            {magic, G, capacities, D}: connect() refuses ranks whose layout differs
-//     ids_in    int64 [G][cap_src]   unique local rows requested by each source rank (its own region)
-//     meta_in   int64 [G][2]         {count, offset of these rows in the requester's unique list}
-//     meta_back int64 [G][2]         per owner: {where this rank's rows start in the owner's compact list, rows accepted}
-//     flags     u64   [3][G]         arrival epochs: ids (by source), rows (by owner), gradients (by source)
-//     uvals     T     [cap_ids][D]   unique rows returned by the owners, in this rank's unique order
-//     grads_in  T     [cap_recv][D]  merged gradient rows of every source, compact, source-major
+//     header    int64 [8]               {magic, G, capacities, D}: connect() refuses ranks whose layout differs
+//     ids_in    int64 [4][G][cap_src]   per prepare slot: unique local rows requested by each source rank
+//     meta_in   int64 [4][G][2]         per slot: {count, offset of these rows in the requester's unique list}
+//     flags     u64   [4][3][G]         per slot: arrival counters of ids (by source), rows (by owner), gradients (by source)
+//     meta_back int64 [G][2]            per owner: {where this rank's rows start in the owner's compact list, rows accepted}
+//     uvals     T     [cap_ids][D]      unique rows returned by the owners, in this rank's unique order
+//     grads_in  T     [cap_recv][D]     merged gradient rows of every source, compact, source-major
 // A step is a fixed sequence of kernels per rank; nothing is read on the host and nothing waits for ALL
-// ranks: a consumer kernel spins only on the flags of the ranks whose data it is about to read.
-//     prepare  (ids only, may run a step ahead on a side stream)   sort plan + de-duplication + split points
-//     lookup   k_send_ids        unique local rows -> owners' ids_in, meta, flag        [NVLink 8 B / unique id]
-//              k_collect_ids     (owner) wait ids flags; compact into recv rows, pad, scatter maps
+// ranks: a consumer kernel spins only on the flags of the ranks whose data it is about to read.  Flags carry
+// the use count of the slot (seq[slot], advanced by prepare), so they never need clearing.
+//     prepare  (ids only: runs a step ahead on a side stream)
+//              sort plan + de-duplication + split points, then
+//              k_send_ids        unique local rows -> owners' ids_in[slot], meta, ids flag   [NVLink 8 B / unique id]
+//     lookup   k_owner_gather    (owner) wait ids flags; rows of the shard -> requesters' uvals; the received ids
+//                                compacted (and padded) for the update's sort plan; meta_back + rows flags from
+//                                the same kernel (every CTA fences its stores)              [NVLink 4D B / unique id]
 //              sort plan of the received rows (side stream: only the update needs it)
-//              k_gather          (owner) rows of the shard -> requesters' uvals, then meta_back + rows flag
-//                                from the same kernel (every thread fences its stores)    [NVLink 4D B / unique id]
 //              k_permute_rows    wait rows flags; expand unique rows to batch order (= merge_ids)
-//     update   k_chunk_reduce<MergeAdd>  local duplicate reduction -> owners' grads_in, then the gradient flag
-//                                from the same kernel                                      [NVLink 4D B / unique id]
+//     update   k_chunk_reduce<MergeAdd>  local duplicate reduction -> owners' grads_in, then the gradient flags
+//                                from the same kernel                                        [NVLink 4D B / unique id]
 //              k_chunk_reduce<Sgd|Adam>  (owner) wait gradient flags; fused update of the shard
-// Buffers are single: the step's own data dependencies order their reuse (a rank cannot send the ids of step
-// i+1 before it has expanded the rows of step i, which every owner sent after collecting the ids of step i, ...).
+// The big buffers are single: the step's own data dependencies order their reuse (a rank cannot store the
+// gradients of step i+1 before it has expanded the rows of step i+1, which every owner sent after its update of
+// step i, ...); the id buffers are per slot because prepare() of step i+1 runs beside step i.
 #include "../../include/b200emb.h"
 
 #include <cstdlib>
@@ -48,18 +51,22 @@ constexpr int kPrepSlots = 4;
 
 struct BlockLayout {
   size_t off_header, off_ids_in, off_meta_in, off_meta_back, off_flags, off_uvals, off_grads_in, total;
+  size_t ids_slot_bytes, meta_slot_bytes, flags_slot_bytes;   // strides between prepare slots
 };
-constexpr long long kBlockMagic = 0x4232303045534831LL;   // every rank's block must have the same layout
+constexpr long long kBlockMagic = 0x4232303045534832LL;   // every rank's block must have the same layout
 
 BlockLayout make_block(int world, int64_t cap_src, int64_t cap_ids, int64_t cap_recv, int64_t d) {
   BlockLayout B{};
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes); return o; };
   B.off_header = take(sizeof(long long) * 8);   // {magic, world, cap_src, cap_ids, cap_recv, d}
-  B.off_ids_in = take(sizeof(int64_t) * world * cap_src);
-  B.off_meta_in = take(sizeof(int64_t) * world * 2);
+  B.ids_slot_bytes = align_up(sizeof(int64_t) * world * cap_src);
+  B.meta_slot_bytes = align_up(sizeof(int64_t) * world * 2);
+  B.flags_slot_bytes = align_up(sizeof(unsigned long long) * 3 * world);
+  B.off_ids_in = take(B.ids_slot_bytes * kPrepSlots);
+  B.off_meta_in = take(B.meta_slot_bytes * kPrepSlots);
   B.off_meta_back = take(sizeof(int64_t) * world * 2);
-  B.off_flags = take(sizeof(unsigned long long) * 3 * world);
+  B.off_flags = take(B.flags_slot_bytes * kPrepSlots);
   B.off_uvals = take(sizeof(float) * cap_ids * d);
   B.off_grads_in = take(sizeof(float) * cap_recv * d);
   B.total = off;
@@ -102,11 +109,10 @@ struct b200emb_shard {
   bool connected = false;
   // private device memory
   char* priv = nullptr;
-  PeerTables T{};
+  PeerTables T[kPrepSlots] = {};         // per prepare slot (the id buffers and the flags are per slot)
   int64_t* recv_local = nullptr;         // [cap_recv] compacted row ids received as owner
   int64_t* seg_start = nullptr;          // [world + 1]
-  float** seg_dst = nullptr;             // [world]
-  unsigned long long* epoch = nullptr;   // the step counter, advanced by k_send_ids
+  unsigned long long* seq = nullptr;     // [kPrepSlots] use count of each slot, advanced by k_send_ids
   unsigned int* done_ctr = nullptr;      // [3] last-CTA detection of k_send_ids / owner gather / local MergeAdd
   int32_t* status = nullptr;
   char* owner_ws = nullptr;
@@ -125,7 +131,7 @@ __device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned l
 // ---- requester: unique local rows -> their owners ---------------------------------------------------------
 // dst region of owner g = ids_in[g] (already offset to this rank's region).  The last CTA to finish publishes,
 // per owner, {count, offset of the first of these rows in this rank's unique list} and the ids flag, and
-// advances the step counter every later kernel of the step reads.
+// advances the slot's use count, which every later kernel of the step reads as the value to wait for / publish.
 __global__ void __launch_bounds__(256)
 k_send_ids(const int64_t* __restrict__ local, const int64_t* __restrict__ bounds, int world, int64_t cap_src,
            PeerTables T, unsigned long long* epoch, unsigned int* done_ctr, int32_t* status) {
@@ -142,18 +148,16 @@ k_send_ids(const int64_t* __restrict__ local, const int64_t* __restrict__ bounds
   __syncthreads();
   __shared__ bool s_last;
   if (threadIdx.x == 0) {
-    __threadfence_system();          // one cumulative fence per CTA, after the barrier that collects its threads' stores
+    __threadfence();                 // cumulative gpu-scope fence per CTA, after the barrier that collects its stores
     s_last = atomicAdd(done_ctr, 1u) == gridDim.x - 1;
   }
   __syncthreads();
   if (!s_last) return;
-  __threadfence_system();
-  if (static_cast<int>(threadIdx.x) < world) {
+  if (static_cast<int>(threadIdx.x) < world) {   // one system-scope release per destination covers ids and meta
     const int g = threadIdx.x;
     const int64_t cnt = min(bounds[g + 1] - bounds[g], cap_src);
     T.meta_in[g][0] = cnt;
     T.meta_in[g][1] = bounds[g];
-    __threadfence_system();
     st_release_sys(T.flag_ids[g], step);
   }
   if (threadIdx.x == 0) {
@@ -162,19 +166,26 @@ k_send_ids(const int64_t* __restrict__ local, const int64_t* __restrict__ bounds
   }
 }
 
-// ---- owner: wait for every source's ids, compact them, build the scatter maps ------------------------------
-// recv[0 .. n_recv) = source 0's rows, source 1's rows, ... ; recv[n_recv .. cap_recv) = pad_id (an id outside the
-// shard: sorts last, is skipped by every consumer).  seg_start[r] = first compact index of source r,
-// seg_dst[r] = where source r wants its rows (its uvals + its offset).  Every CTA waits for the flags and
-// derives the (tiny) prefix itself, so the grid needs no internal synchronisation.
-__global__ void __launch_bounds__(256)
-k_collect_ids(const int64_t* __restrict__ ids_in, const int64_t* __restrict__ meta_in,
-              const unsigned long long* __restrict__ flag_ids, const unsigned long long* epoch, int world,
-              int64_t cap_src, int64_t cap_recv, int64_t pad_id, int64_t d, float* const* __restrict__ peer_uvals,
-              int64_t* __restrict__ recv, int64_t* __restrict__ seg_start, float** __restrict__ seg_dst,
-              int32_t* status) {
+// ---- owner: wait for every source's ids; gather their rows straight into the requesters' buffers -----------
+// Compact index k runs over source 0's rows, source 1's rows, ...: row k is read from the shard and stored at
+// (source r's uvals) + (its offset + k - start[r]) * D.  On the way the ids are written to recv[k] (the list the
+// update's sort plan needs), recv[n_recv .. cap_recv) = pad_id (an id outside the shard: sorts last, skipped by
+// every consumer), and seg_start[] = the prefix.  Every CTA waits for the flags and derives the (tiny) prefix
+// itself; the rows flags (with each requester's start and accepted count) leave from this same kernel.
+template <int LPR, int NV, bool VEC>
+__global__ void __launch_bounds__(kBlock, 4)
+k_owner_gather(const float* __restrict__ table, int64_t height, int d, const int64_t* __restrict__ ids_in,
+               const int64_t* __restrict__ meta_in, const unsigned long long* __restrict__ flag_ids,
+               const unsigned long long* seq, int world, int64_t cap_src, int64_t cap_recv, int64_t pad_id,
+               float* const* __restrict__ peer_uvals, int64_t* __restrict__ recv, int64_t* __restrict__ seg_start,
+               SignalSpec sig, int32_t* status) {
+  constexpr int EPV = Epv<float, VEC>::value;
+  constexpr int kGroups = kBlock / LPR;
+  constexpr int kRows = 4;
   __shared__ int64_t s_start[kMaxWorld + 1];
-  wait_for_flags(flag_ids, epoch, world, status);
+  __shared__ int64_t s_off[kMaxWorld];
+  __shared__ float* s_dst[kMaxWorld];
+  wait_for_flags(flag_ids, seq, world, status);
   if (threadIdx.x == 0) {
     int64_t run = 0;
     for (int r = 0; r < world; ++r) {
@@ -188,23 +199,71 @@ k_collect_ids(const int64_t* __restrict__ ids_in, const int64_t* __restrict__ me
     }
     s_start[world] = run;
   }
+  if (static_cast<int>(threadIdx.x) < world) {
+    s_off[threadIdx.x] = meta_in[2 * threadIdx.x + 1];
+    s_dst[threadIdx.x] = peer_uvals[threadIdx.x];
+  }
   __syncthreads();
-  if (blockIdx.x == 0) {
-    if (static_cast<int>(threadIdx.x) <= world) seg_start[threadIdx.x] = s_start[threadIdx.x];
-    if (static_cast<int>(threadIdx.x) < world)
-      seg_dst[threadIdx.x] = peer_uvals[threadIdx.x] + meta_in[2 * threadIdx.x + 1] * d;
-  }
+  if (blockIdx.x == 0 && static_cast<int>(threadIdx.x) <= world) seg_start[threadIdx.x] = s_start[threadIdx.x];
   const int64_t total = s_start[world];
-  for (int64_t k = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; k < cap_recv;
-       k += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-    int64_t v = pad_id;
+  const int l = threadIdx.x % LPR;
+  const int64_t group = static_cast<int64_t>(blockIdx.x) * kGroups + threadIdx.x / LPR;
+  const int64_t num_groups = static_cast<int64_t>(gridDim.x) * kGroups;
+  // id and destination of compact index k (software-pipelined: the next batch's ids are requested while this
+  // batch's rows are in flight, so the id -> row dependency costs one round trip per batch, not two)
+  const auto locate = [&](int64_t k, int64_t& id, float*& dst) {
+    id = pad_id;
+    dst = nullptr;
     if (k < total) {
-      int r = 0;
-      while (r + 1 < world && k >= s_start[r + 1]) ++r;
-      v = ids_in[static_cast<int64_t>(r) * cap_src + (k - s_start[r])];
+      int src = 0;
+      while (src + 1 < world && k >= s_start[src + 1]) ++src;
+      const int64_t j = k - s_start[src];
+      id = ids_in[static_cast<int64_t>(src) * cap_src + j];
+      dst = s_dst[src] + (s_off[src] + j) * d;
     }
-    recv[k] = v;
+  };
+  int64_t nid[kRows];
+  float* ndst[kRows];
+#pragma unroll
+  for (int r = 0; r < kRows; ++r) locate(group + r * num_groups, nid[r], ndst[r]);
+  for (int64_t base = group; base < cap_recv; base += num_groups * kRows) {
+    int64_t id[kRows];
+    float* dst[kRows];
+    bool copy[kRows];
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) {
+      const int64_t k = base + r * num_groups;
+      id[r] = nid[r];
+      dst[r] = ndst[r];
+      copy[r] = dst[r] != nullptr && id[r] >= 0 && id[r] < height;
+      if (l == 0 && k < cap_recv) recv[k] = id[r];
+    }
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) locate(base + num_groups * kRows + r * num_groups, nid[r], ndst[r]);
+    for (int col0 = 0; col0 < d; col0 += LPR * NV * EPV) {
+      float v[kRows][NV][EPV];
+#pragma unroll
+      for (int r = 0; r < kRows; ++r)
+#pragma unroll
+        for (int kk = 0; kk < NV; ++kk) {
+          const int col = col0 + (l + kk * LPR) * EPV;
+          if (copy[r] && col < d) {
+            load_vec<float, VEC>(table + id[r] * d + col, v[r][kk]);
+          } else {
+#pragma unroll
+            for (int e = 0; e < EPV; ++e) v[r][kk][e] = 0.f;
+          }
+        }
+#pragma unroll
+      for (int r = 0; r < kRows; ++r)
+#pragma unroll
+        for (int kk = 0; kk < NV; ++kk) {
+          const int col = col0 + (l + kk * LPR) * EPV;
+          if (dst[r] != nullptr && col < d) store_vec_stream<float, VEC>(dst[r] + col, v[r][kk]);
+        }
+    }
   }
+  signal_peers(sig.flag_dst, sig.payload_dst, sig.starts, sig.epoch, sig.done_ctr, sig.world);
 }
 
 // ---- producer side of a flag: optional payload {a[r], b[r+1]-b[r]}, then the flag, one thread per destination ----
@@ -216,7 +275,6 @@ __global__ void k_signal(int world, int64_t* const* __restrict__ payload_dst, co
     payload_dst[r][0] = starts[r];                   // first compact index of rank r's rows on this owner
     payload_dst[r][1] = starts[r + 1] - starts[r];   // how many of them the owner accepted
   }
-  __threadfence_system();
   st_release_sys(flag_dst[r], *epoch);
 }
 
@@ -270,8 +328,8 @@ int b200emb_shard_create(int world, int rank, int64_t height, int64_t d, int opt
   sh->prep_ws_bytes = ws_upto(sh->cap_ids);
   sh->owner_ws_bytes = ws_upto(sh->cap_recv);
   const size_t w = static_cast<size_t>(world);
-  size_t need = 8 * align_up(sizeof(void*) * w) + align_up(sizeof(int64_t) * sh->cap_recv) +
-                align_up(sizeof(int64_t) * (w + 1)) + align_up(sizeof(float*) * w) + 3 * 256 +
+  size_t need = kPrepSlots * 8 * align_up(sizeof(void*) * w) + align_up(sizeof(int64_t) * sh->cap_recv) +
+                align_up(sizeof(int64_t) * (w + 1)) + 3 * 256 +
                 align_up(sh->owner_ws_bytes) +
                 kPrepSlots * (align_up(sh->prep_ws_bytes) + 2 * align_up(sizeof(int64_t) * sh->cap_ids) +
                               align_up(sizeof(int64_t) * (w + 1)) + 256);
@@ -286,18 +344,19 @@ int b200emb_shard_create(int world, int rank, int64_t height, int64_t d, int opt
     return B200EMB_E_CUDA;
   }
   char* cur = sh->priv;
-  sh->T.ids_in = carve<int64_t*>(cur, w);
-  sh->T.meta_in = carve<int64_t*>(cur, w);
-  sh->T.flag_ids = carve<unsigned long long*>(cur, w);
-  sh->T.uvals = carve<float*>(cur, w);
-  sh->T.meta_back = carve<int64_t*>(cur, w);
-  sh->T.flag_rows = carve<unsigned long long*>(cur, w);
-  sh->T.grads_in = carve<float*>(cur, w);
-  sh->T.flag_grads = carve<unsigned long long*>(cur, w);
+  for (int t = 0; t < kPrepSlots; ++t) {
+    sh->T[t].ids_in = carve<int64_t*>(cur, w);
+    sh->T[t].meta_in = carve<int64_t*>(cur, w);
+    sh->T[t].flag_ids = carve<unsigned long long*>(cur, w);
+    sh->T[t].uvals = carve<float*>(cur, w);
+    sh->T[t].meta_back = carve<int64_t*>(cur, w);
+    sh->T[t].flag_rows = carve<unsigned long long*>(cur, w);
+    sh->T[t].grads_in = carve<float*>(cur, w);
+    sh->T[t].flag_grads = carve<unsigned long long*>(cur, w);
+  }
   sh->recv_local = carve<int64_t>(cur, sh->cap_recv);
   sh->seg_start = carve<int64_t>(cur, w + 1);
-  sh->seg_dst = carve<float*>(cur, w);
-  sh->epoch = carve<unsigned long long>(cur, 1);
+  sh->seq = carve<unsigned long long>(cur, kPrepSlots);
   sh->done_ctr = carve<unsigned int>(cur, 3);
   sh->status = carve<int32_t>(cur, 1);
   sh->owner_ws = cur; cur += align_up(sh->owner_ws_bytes);
@@ -337,24 +396,27 @@ static int finish_connect(b200emb_shard* sh) {
       return B200EMB_E_INVALID;   // create() was called with different sizes on that rank
   }
   std::vector<void*> h(8 * static_cast<size_t>(w));
-  for (int g = 0; g < w; ++g) {
-    char* pb = sh->peer[g];
-    h[0 * w + g] = pb + L.off_ids_in + sizeof(int64_t) * static_cast<size_t>(me) * sh->cap_src;
-    h[1 * w + g] = pb + L.off_meta_in + sizeof(int64_t) * 2 * me;
-    h[2 * w + g] = pb + L.off_flags + sizeof(unsigned long long) * (0 * w + me);
-    h[3 * w + g] = pb + L.off_uvals;
-    h[4 * w + g] = pb + L.off_meta_back + sizeof(int64_t) * 2 * me;
-    h[5 * w + g] = pb + L.off_flags + sizeof(unsigned long long) * (1 * w + me);
-    h[6 * w + g] = pb + L.off_grads_in;
-    h[7 * w + g] = pb + L.off_flags + sizeof(unsigned long long) * (2 * w + me);
-  }
-  void* dst[8] = {sh->T.ids_in, sh->T.meta_in, sh->T.flag_ids, sh->T.uvals,
-                  sh->T.meta_back, sh->T.flag_rows, sh->T.grads_in, sh->T.flag_grads};
-  for (int t = 0; t < 8; ++t)
-    if (cudaMemcpy(dst[t], &h[static_cast<size_t>(t) * w], sizeof(void*) * w, cudaMemcpyHostToDevice) != cudaSuccess) {
-      cudaGetLastError();
-      return B200EMB_E_CUDA;
+  for (int t = 0; t < kPrepSlots; ++t) {
+    for (int g = 0; g < w; ++g) {
+      char* pb = sh->peer[g];
+      char* fl = pb + L.off_flags + L.flags_slot_bytes * t;
+      h[0 * w + g] = pb + L.off_ids_in + L.ids_slot_bytes * t + sizeof(int64_t) * static_cast<size_t>(me) * sh->cap_src;
+      h[1 * w + g] = pb + L.off_meta_in + L.meta_slot_bytes * t + sizeof(int64_t) * 2 * me;
+      h[2 * w + g] = fl + sizeof(unsigned long long) * (0 * w + me);
+      h[3 * w + g] = pb + L.off_uvals;
+      h[4 * w + g] = pb + L.off_meta_back + sizeof(int64_t) * 2 * me;
+      h[5 * w + g] = fl + sizeof(unsigned long long) * (1 * w + me);
+      h[6 * w + g] = pb + L.off_grads_in;
+      h[7 * w + g] = fl + sizeof(unsigned long long) * (2 * w + me);
     }
+    void* dst[8] = {sh->T[t].ids_in, sh->T[t].meta_in, sh->T[t].flag_ids, sh->T[t].uvals,
+                    sh->T[t].meta_back, sh->T[t].flag_rows, sh->T[t].grads_in, sh->T[t].flag_grads};
+    for (int k = 0; k < 8; ++k)
+      if (cudaMemcpy(dst[k], &h[static_cast<size_t>(k) * w], sizeof(void*) * w, cudaMemcpyHostToDevice) != cudaSuccess) {
+        cudaGetLastError();
+        return B200EMB_E_CUDA;
+      }
+  }
   sh->connected = true;
   return B200EMB_OK;
 }
@@ -385,14 +447,21 @@ int b200emb_shard_connect_ptrs(b200emb_shard_t* sh, void* const* blocks) {
 
 int b200emb_shard_prepare(b200emb_shard_t* sh, int slot, const int64_t* ids, int64_t n, void* stream) {
   if (!sh || slot < 0 || slot >= kPrepSlots || n < 0 || n > sh->cap_ids || (n > 0 && !ids)) return B200EMB_E_INVALID;
+  if (!sh->connected) return B200EMB_E_INVALID;
   PrepSlot& p = sh->slots[slot];
   p.ids = ids;
   p.n = n;
-  return b200emb_plan_unique_rows(ids, n, sh->height, sh->world, p.ukeys, p.n_unique, p.bounds, nullptr, p.local,
-                                  p.ws, sh->prep_ws_bytes, sh->status, stream);
+  const int rc = b200emb_plan_unique_rows(ids, n, sh->height, sh->world, p.ukeys, p.n_unique, p.bounds, nullptr,
+                                          p.local, p.ws, sh->prep_ws_bytes, sh->status, stream);
+  if (rc != B200EMB_OK) return rc;
+  // the id exchange needs the ids only, too: the owners find them waiting when the step starts
+  const int grid = static_cast<int>(std::min<int64_t>(std::max<int64_t>(ceil_div(n, 256), 1), 148 * 4));
+  k_send_ids<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(p.local, p.bounds, sh->world, sh->cap_src, sh->T[slot],
+                                                                 sh->seq + slot, sh->done_ctr, sh->status);
+  return cudaGetLastError() == cudaSuccess ? B200EMB_OK : B200EMB_E_CUDA;
 }
 
-// phases of lookup: 0 send ids | 1 collect + owner plan | 2 owner gather + signal | 3 expand
+// phases of lookup: 0 (nothing: the ids went out in prepare) | 1 owner gather + flags | 2 fork owner sort plan | 3 expand
 int b200emb_shard_lookup_phases(b200emb_shard_t* sh, int slot, float* out, void* stream, int first, int last) {
   if (!sh || !sh->connected || slot < 0 || slot >= kPrepSlots || first < 0 || last > 3 || first > last) return B200EMB_E_INVALID;
   PrepSlot& p = sh->slots[slot];
@@ -400,21 +469,33 @@ int b200emb_shard_lookup_phases(b200emb_shard_t* sh, int slot, float* out, void*
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int w = sh->world;
   const BlockLayout& L = sh->L;
-  unsigned long long* flags = reinterpret_cast<unsigned long long*>(sh->block + L.off_flags);
+  unsigned long long* flags = reinterpret_cast<unsigned long long*>(sh->block + L.off_flags + L.flags_slot_bytes * slot);
+  const unsigned long long* seq = sh->seq + slot;
   cudaError_t e = cudaSuccess;
-  if (first <= 0 && 0 <= last) {
-    const int grid = static_cast<int>(std::min<int64_t>(std::max<int64_t>(ceil_div(p.n, 256), 1), 148 * 4));
-    k_send_ids<<<grid, 256, 0, s>>>(p.local, p.bounds, w, sh->cap_src, sh->T, sh->epoch, sh->done_ctr, sh->status);
+  if (first <= 1 && 1 <= last) {
+    // the rows and the rows flags leave from the same kernel: every CTA fences its peer stores before the last
+    // one raises the flags (and tells each requester where its rows sit in this owner's compact list)
+    SignalSpec sg;
+    sg.flag_dst = sh->T[slot].flag_rows;
+    sg.payload_dst = sh->T[slot].meta_back;
+    sg.starts = sh->seg_start;
+    sg.epoch = seq;
+    sg.done_ctr = sh->done_ctr + 1;
+    sg.world = w;
+    const int64_t* ids_in = reinterpret_cast<const int64_t*>(sh->block + L.off_ids_in + L.ids_slot_bytes * slot);
+    const int64_t* meta_in = reinterpret_cast<const int64_t*>(sh->block + L.off_meta_in + L.meta_slot_bytes * slot);
+    const bool aligned = is_aligned16(sh->shard) && (sh->d % 4) == 0;
+    dispatch_row_shape<float>(sh->d, aligned, [&]<int LPR, int NV, bool VEC>() {
+      constexpr int kGroups = kBlock / LPR;
+      const int grid = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(ceil_div(sh->cap_recv, kGroups), 148 * 4)));
+      k_owner_gather<LPR, NV, VEC><<<grid, kBlock, 0, s>>>(sh->shard, sh->hs, static_cast<int>(sh->d), ids_in, meta_in,
+                                                          flags, seq, w, sh->cap_src, sh->cap_recv, sh->hs,
+                                                          sh->T[slot].uvals, sh->recv_local, sh->seg_start, sg, sh->status);
+    });
     if ((e = cudaGetLastError()) != cudaSuccess) return fail(e);
   }
-  if (first <= 1 && 1 <= last) {
-    const int cgrid = static_cast<int>(std::min<int64_t>(std::max<int64_t>(ceil_div(sh->cap_recv, 1024), 1), 148 * 2));
-    k_collect_ids<<<cgrid, 256, 0, s>>>(reinterpret_cast<const int64_t*>(sh->block + L.off_ids_in),
-                                     reinterpret_cast<const int64_t*>(sh->block + L.off_meta_in), flags, sh->epoch, w,
-                                     sh->cap_src, sh->cap_recv, sh->hs, sh->d, sh->T.uvals, sh->recv_local,
-                                     sh->seg_start, sh->seg_dst, sh->status);
-    if ((e = cudaGetLastError()) != cudaSuccess) return fail(e);
-    // the update's sort plan needs the received ids only: build it beside the row exchange
+  if (first <= 2 && 2 <= last) {
+    // the update's sort plan needs the received ids only: build it beside the expansion and the local MergeAdd
     if ((e = cudaEventRecord(sh->ev_fork, s)) != cudaSuccess) return fail(e);
     if ((e = cudaStreamWaitEvent(sh->side, sh->ev_fork, 0)) != cudaSuccess) return fail(e);
     const Workspace OW = make_workspace(sh->cap_recv, sh->d, 4);
@@ -422,27 +503,13 @@ int b200emb_shard_lookup_phases(b200emb_shard_t* sh, int slot, float* out, void*
     if (e != cudaSuccess) return fail(e);
     if ((e = cudaEventRecord(sh->ev_plan, sh->side)) != cudaSuccess) return fail(e);
   }
-  if (first <= 2 && 2 <= last) {
-    // the rows and the rows flag leave from the same kernel: every thread fences its peer stores before the last
-    // CTA raises the flags (and tells each requester where its rows sit in this owner's compact list)
-    SignalSpec sg;
-    sg.flag_dst = sh->T.flag_rows;
-    sg.payload_dst = sh->T.meta_back;
-    sg.starts = sh->seg_start;
-    sg.epoch = sh->epoch;
-    sg.done_ctr = sh->done_ctr + 1;
-    sg.world = w;
-    e = launch_gather<float>(sh->shard, sh->hs, sh->d, sh->recv_local, sh->cap_recv, -1, nullptr, nullptr, s,
-                             sh->seg_start, sh->seg_dst, w, sg);
-    if (e != cudaSuccess) return fail(e);
-  }
   if (first <= 3 && 3 <= last && p.n > 0) {
     const Workspace PW = make_workspace(p.n, 1, 4);
     SortedPlan plan = plan_view(p.n, sh->plan_h, p.ws, PW);
     plan.perm = reinterpret_cast<const uint32_t*>(p.ws + PW.off_perm[(plan.passes & 1) ^ 1]);   // the inverse map
     WaitSpec wt;
     wt.flags = flags + w;
-    wt.epoch = sh->epoch;
+    wt.epoch = seq;
     wt.world = w;
     wt.status = sh->status;
     e = launch_permute_rows<float>(reinterpret_cast<const float*>(sh->block + L.off_uvals), plan,
@@ -468,7 +535,8 @@ int b200emb_shard_update_phases(b200emb_shard_t* sh, int slot, const float* d_ou
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int w = sh->world;
   const BlockLayout& L = sh->L;
-  unsigned long long* flags = reinterpret_cast<unsigned long long*>(sh->block + L.off_flags);
+  unsigned long long* flags = reinterpret_cast<unsigned long long*>(sh->block + L.off_flags + L.flags_slot_bytes * slot);
+  const unsigned long long* seq = sh->seq + slot;
   cudaError_t e = cudaSuccess;
   if (first <= 0 && 0 <= last) {
     if (p.n > 0) {
@@ -478,19 +546,19 @@ int b200emb_shard_update_phases(b200emb_shard_t* sh, int slot, const float* d_ou
       a.param = const_cast<float*>(d_out);   // unused: every merged row goes through the scatter map
       a.uidx = reinterpret_cast<const uint32_t*>(p.ws + PW.off_uidx);
       a.shard_bounds = p.bounds;
-      a.shard_dst = sh->T.grads_in;
+      a.shard_dst = sh->T[slot].grads_in;
       a.shard_meta = reinterpret_cast<const int64_t*>(sh->block + L.off_meta_back);
       a.shards = w;
       a.dst_aligned16 = (sh->d % 4) == 0;
-      a.signal.flag_dst = sh->T.flag_grads;      // merged rows and their flag leave from the same kernel
-      a.signal.epoch = sh->epoch;
+      a.signal.flag_dst = sh->T[slot].flag_grads;      // merged rows and their flag leave from the same kernel
+      a.signal.epoch = seq;
       a.signal.done_ctr = sh->done_ctr + 2;
       a.signal.world = w;
       const SortedPlan plan = plan_view(p.n, sh->plan_h, p.ws, PW);
       e = launch_update<float>(plan, d_out, p.n, sh->d, sh->plan_h, a, false, p.ws, PW, sh->status, s);
       if (e != cudaSuccess) return fail(e);
     } else {   // an empty batch still has to tell the owners that nothing is coming
-      k_signal<<<1, ((w + 31) / 32) * 32, 0, s>>>(w, nullptr, nullptr, sh->T.flag_grads, sh->epoch);
+      k_signal<<<1, ((w + 31) / 32) * 32, 0, s>>>(w, nullptr, nullptr, sh->T[slot].flag_grads, seq);
       if ((e = cudaGetLastError()) != cudaSuccess) return fail(e);
     }
   }
@@ -507,7 +575,7 @@ int b200emb_shard_update_phases(b200emb_shard_t* sh, int slot, const float* d_ou
     a.beta2_pow = beta2_pow;
     a.beta1 = beta1; a.beta2 = beta2; a.epsilon = epsilon;
     a.wait.flags = flags + 2 * w;
-    a.wait.epoch = sh->epoch;
+    a.wait.epoch = seq;
     a.wait.world = w;
     a.wait.status = sh->status;
     const SortedPlan plan = plan_view(sh->cap_recv, sh->hs, sh->owner_ws, OW);
@@ -539,7 +607,7 @@ int b200emb_shard_debug_ptrs(b200emb_shard_t* sh, int slot, void** out6) {
   out6[1] = sh->slots[slot].n_unique;
   out6[2] = sh->seg_start;
   out6[3] = sh->recv_local;
-  out6[4] = sh->epoch;
+  out6[4] = sh->seq + slot;
   out6[5] = sh->status;
   return B200EMB_OK;
 }

@@ -494,7 +494,7 @@ cudaError_t launch_plan(const int64_t* rows, int64_t n, int64_t height, char* ws
   // optional: the whole sort in one 16-CTA cluster launch (cluster_sort.cu).  Measured slower
   // than the multi-launch path on B200, so it is opt-in.
   static const bool use_cluster = std::getenv("B200EMB_CLUSTER_SORT") != nullptr;
-  if (use_cluster && km.shards <= 1 && cluster_sort_fits(n)) {
+  if (use_cluster && keymap == nullptr && cluster_sort_fits(n)) {   // the cluster kernel sorts raw ids: no key map
     const int cpasses = static_cast<int>(ceil_div(key_bits(height), kRadixBits));
     // the cluster kernel always uses 8-bit digits; it writes straight into the buffers the
     // digit plan's parity selects

@@ -65,6 +65,9 @@ def test_sharded_save_load_is_global_row_order(ck, tmp_path):
     with open(path, "rb") as f:
         back, lod = ck.read_lod_tensor(f)
     assert lod == [] and np.array_equal(back, full)
+    # the gather-through-rank-0 writer produces the same bytes as the every-rank-writes-its-rows one
+    ck.save_sharded(path + ".g", torch.from_numpy(full), v, 0, 1, parallel=False)
+    assert open(path, "rb").read() == open(path + ".g", "rb").read()
     # a reader with 3 ranks takes rows r, r+3, ... (owner = id % G, operators/split_ids_op.h:47)
     for rank in range(3):
         shard, height = ck.load_sharded(path, rank, 3, "cpu")

@@ -143,7 +143,7 @@ def test_engine_ranks_on_one_gpu(capi, world, optimizer):
         assert st & capi.STATUS_BARRIER_TIMEOUT == 0 and st & capi.STATUS_SHARD_OVERFLOW == 0
         assert (st & 2) == (2 if r == 0 else 0)      # rank 0's out-of-range ids were flagged by its plan
         bounds, nu, seg, epoch = eng[r].debug_views((steps - 1) % 4)
-        assert int(epoch.item()) == steps and int(bounds[-1].item()) == int(nu.item())
+        assert int(epoch.item()) == 1 and int(bounds[-1].item()) == int(nu.item())   # every slot was used once
     for e in eng:
         e.destroy()
 
