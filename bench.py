@@ -9,7 +9,8 @@ One "step" = one pass of the hot path over one synthetic batch:
         forward gather of the batch's rows, then the sort-by-id + duplicate-row reduction fused
         with the in-place SGD row update (the SelectedRows gradient aliases ids/dOut: zero copy).
   N>1 : configs[3] — 100M x 64 table row-sharded over the N GPUs (owner = id % N), the same
-        per-GPU batch; id all-to-all -> gather -> row all-to-all; grad all-to-all -> fused update.
+        per-GPU batch, through the row-sharded step engine (bench_sharded.py): ids -> owners, owner gather ->
+        requesters, local MergeAdd -> owners, fused owner update; plus a batch sweep and a parity epilogue.
 Prints ONE JSON line (rank 0).  metric = lookups+updates/s = ids processed per second, whole job.
 """
 import argparse
@@ -159,7 +160,10 @@ def run_reference_arm(args):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": {"workload": workload_name(args.gpus), "table": [v, d], "ids_per_step": n,
-                   "optimizer": opt, "note": "reference CPU kernels (%s), single thread" % res["kind"]},
+                   "optimizer": opt, "note": "reference CPU kernels (%s), single thread" % res["kind"] + (
+                       "; one rank's per-step batch (the same %d ids per GPU as the sharded arm) against a table of "
+                       "V/G rows: the reference replicates the table per device and its CPU kernels are single-threaded, "
+                       "so this is the CPU cost of ONE replica's step, not of the whole job" % n if args.gpus > 1 else "")},
         "cpu_baseline": {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")},
         "e2e": {"value": res["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
