@@ -318,14 +318,13 @@ __device__ __forceinline__ void close_chain(int c, int len, uint32_t key, uint32
 // a CTA then splits its adjusted range evenly over its groups.
 struct ChunkGeom {
   int n, chunk, slack;
-  int batch;     // rows per ring batch (timing only: the summation order does not depend on it)
 };
 
-// The shared-memory ring holds kRingStages batches of `batch` rows (a launch parameter, <= kMaxBatch: the
-// batch loops are unrolled kMaxBatch times and predicated).
+// The shared-memory ring holds kRingStages batches of kBatch rows; kBatch is a compile-time property of the
+// row shape (a launch-time batch with predicated, fully unrolled loops cost the one-row-per-batch Adam shapes
+// 14 %), sized so that the ring of a CTA stays near 48 KB and three CTAs fit an SM for the common shapes.
 constexpr int kRingStages = 3;
-constexpr int kMaxBatch = 4;
-constexpr int kRingTargetBytes = 48 * 1024;   // default ring size per CTA: three CTAs fit an SM for the common shapes
+constexpr int kRingTargetBytes = 48 * 1024;
 template <typename T, UpdateOp OP, int NV, bool VEC>
 struct Ring {
   static constexpr int kVB = Epv<T, VEC>::value * static_cast<int>(sizeof(T));   // bytes per lane per vector
@@ -337,16 +336,9 @@ struct Ring {
   // one more slot holds the state of the segment a group leaves open (single-state consumers only: for
   // Adam / Adagrad that slot would cost a resident CTA)
   static constexpr bool kTailInRing = kStateInRing && NumState<OP>::value == 1;
-  static int batch_for(int target_bytes) {
-    const int fit = target_bytes / (kRingStages * kSlotBytes);
-    return fit >= 4 ? 4 : (fit >= 2 ? 2 : 1);
-  }
-  static size_t bytes_for(int batch) {
-    return static_cast<size_t>(kRingStages * batch + (kTailInRing ? 1 : 0)) * kSlotBytes;
-  }
-  static __device__ __forceinline__ uint32_t bytes_for_dev(int batch) {
-    return static_cast<uint32_t>(kRingStages * batch + (kTailInRing ? 1 : 0)) * kSlotBytes;
-  }
+  static constexpr int kFit = kRingTargetBytes / (kRingStages * kSlotBytes);
+  static constexpr int kBatch = kFit >= 4 ? 4 : (kFit >= 2 ? 2 : 1);
+  static constexpr int kBytes = (kRingStages * kBatch + (kTailInRing ? 1 : 0)) * kSlotBytes;
 };
 
 __device__ __forceinline__ void lds_vec(uint32_t addr, float (&v)[4]) {
@@ -383,11 +375,11 @@ __device__ __forceinline__ void chunk_reduce_body(const uint32_t* __restrict__ s
   constexpr int NS = NumState<OP>::value;
   using RG = Ring<T, OP, NV, VEC>;
   constexpr int VB = RG::kVB, S = kRingStages;
-  const int B = G.batch;
+  constexpr int B = RG::kBatch;
   constexpr uint32_t kVecStride = kBlock * VB;                 // between the vectors of one slot
   constexpr uint32_t kPartStride = NV * kVecStride;            // between the parts (row, state rows) of one slot
   constexpr uint32_t kSlotStride = RG::kSlotBytes;
-  const int kTailSlot = S * B;                                 // state of the segment a group leaves open
+  constexpr int kTailSlot = S * B;                                 // state of the segment a group leaves open
   using A = Arith<T>;
   const int n = G.n;
   const int stride = GPC * G.chunk;                            // nominal sorted elements per CTA
@@ -398,7 +390,7 @@ __device__ __forceinline__ void chunk_reduce_body(const uint32_t* __restrict__ s
   // ring[slot][part][vector][thread], filled by cp.async: a thread only ever touches its own column, so the
   // ring needs no barrier, only cp.async.wait_group
   const uint32_t ring = smem_addr(smem_raw) + tid * VB;
-  T* s_head = reinterpret_cast<T*>(smem_raw + RG::bytes_for_dev(B));    // [GPC][COLS]
+  T* s_head = reinterpret_cast<T*>(smem_raw + RG::kBytes);    // [GPC][COLS]
   T* s_tail = s_head + GPC * COLS;                            // [GPC][COLS]
   uint32_t* s_key = reinterpret_cast<uint32_t*>(s_tail + GPC * COLS);  // [win]
   uint32_t* s_pos = s_key + win;                              // [win] original position | kCloses | kDirect
@@ -572,9 +564,9 @@ __device__ __forceinline__ void chunk_reduce_body(const uint32_t* __restrict__ s
         const int i0 = gs + bi * B;
         const uint32_t stage_addr = ring + (bi % S) * (B * kSlotStride);
 #pragma unroll
-        for (int q = 0; q < kMaxBatch; ++q) {
+        for (int q = 0; q < B; ++q) {
           const int idx = i0 + q;
-          if (q < B && idx < ge) {
+          if (idx < ge) {
             const uint32_t pw = s_pos[idx - w0];
             const T* src = value + static_cast<int64_t>(pw & kPosMask) * d;
             const uint32_t slot_addr = stage_addr + q * kSlotStride;
@@ -601,9 +593,9 @@ __device__ __forceinline__ void chunk_reduce_body(const uint32_t* __restrict__ s
         const int i0 = gs + bi * B;
         const uint32_t stage_addr = ring + (bi % S) * (B * kSlotStride);
 #pragma unroll
-        for (int q = 0; q < kMaxBatch; ++q) {
+        for (int q = 0; q < B; ++q) {
           const int idx = i0 + q;
-          if (q < B && idx < ge) {
+          if (idx < ge) {
             const uint32_t slot_addr = stage_addr + q * kSlotStride;
 #pragma unroll
             for (int kk = 0; kk < NV; ++kk) {
@@ -805,17 +797,81 @@ k_chunk_reduce(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ p
 }
 
 // ------------------------------------------------------------------------------------------
-// Bit-exact order mode: one lane group per unique row, duplicates in input order.
+// Bit-exact order mode: the duplicates of a row are added strictly in input order, so the adds of one element
+// form one dependent chain — but the LOADS do not, and neither do different elements.  Rows with up to kLongSeg
+// duplicates are walked by one lane group each (k_segment_det); a group that finds more than that drops the row
+// (nothing written yet) into a list for k_long_segment_det below.  Same arithmetic, same order, same bits.
+constexpr int kLongSeg = 64;
+
+template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
+__device__ __forceinline__ void det_begin(const Params<T>& P, uint32_t key, int col0, int l,
+                                          T (&acc)[NV][Epv<T, VEC>::value]) {
+  constexpr int EPV = Epv<T, VEC>::value;
+  if constexpr (OP == UpdateOp::kSgd || OP == UpdateOp::kAddToTensor) {
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int col = col0 + (l + k * LPR) * EPV;
+      if (col < P.d) load_vec<T, VEC>(P.param + static_cast<int64_t>(key) * P.d + col, acc[k]);
+      else {
+#pragma unroll
+        for (int e = 0; e < EPV; ++e) acc[k][e] = T(0);
+      }
+    }
+  } else {
+    zero_acc<T, NV, EPV>(acc);  // MergeAdd starts from +0.0 (SetConstant, selected_rows_functor.cc:211-212)
+  }
+}
+
+template <typename T, UpdateOp OP, int NV, int EPV>
+__device__ __forceinline__ void det_add(T (&acc)[NV][EPV], const T (&r)[NV][EPV], T lr) {
+  using A = Arith<T>;
+#pragma unroll
+  for (int k = 0; k < NV; ++k)
+#pragma unroll
+    for (int e = 0; e < EPV; ++e) {
+      if constexpr (OP == UpdateOp::kSgd) acc[k][e] = A::sub(acc[k][e], A::mul(lr, r[k][e]));  // sgd_op.h:77-79
+      else acc[k][e] = A::add(acc[k][e], r[k][e]);
+    }
+}
+
+// the same step with the product lr * g already formed (by whichever thread fetched the row: same operands, same bits)
+template <typename T, UpdateOp OP, int NV, int EPV>
+__device__ __forceinline__ void det_add_scaled(T (&acc)[NV][EPV], const T (&r)[NV][EPV]) {
+  using A = Arith<T>;
+#pragma unroll
+  for (int k = 0; k < NV; ++k)
+#pragma unroll
+    for (int e = 0; e < EPV; ++e) {
+      if constexpr (OP == UpdateOp::kSgd) acc[k][e] = A::sub(acc[k][e], r[k][e]);
+      else acc[k][e] = A::add(acc[k][e], r[k][e]);
+    }
+}
+
+template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
+__device__ __forceinline__ void det_end(const Params<T>& P, uint32_t key, uint32_t first_pos, int col0, int l,
+                                        T (&acc)[NV][Epv<T, VEC>::value]) {
+  constexpr int EPV = Epv<T, VEC>::value;
+  if constexpr (OP == UpdateOp::kSgd || OP == UpdateOp::kAddToTensor) {
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int col = col0 + (l + k * LPR) * EPV;
+      if (col < P.d) store_vec<T, VEC>(P.param + static_cast<int64_t>(key) * P.d + col, acc[k]);
+    }
+  } else {
+    consume<T, OP, LPR, NV, VEC>(P, key, first_pos, col0, l, acc);
+  }
+}
+
 template <typename T, UpdateOp OP, int LPR, int NV, bool VEC>
 __global__ void __launch_bounds__(kBlock)
 k_segment_det(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ perm, int n,
               const uint32_t* __restrict__ seg_start, const PlanHeader* hdr,
-              const T* __restrict__ value, Params<T> P) {
+              const T* __restrict__ value, Params<T> P, uint32_t* __restrict__ long_list,
+              uint32_t* __restrict__ long_count) {
   constexpr int EPV = Epv<T, VEC>::value;
   constexpr int GPC = kBlock / LPR;
   constexpr int COLS = LPR * NV * EPV;
   constexpr int kPrefetch = NV >= 4 ? 2 : (NV == 2 ? 4 : 8);
-  using A = Arith<T>;
   const int l = threadIdx.x % LPR;
   const int d = P.d;
   wait_for_flags(P.wait.flags, P.wait.epoch, P.wait.world, P.wait.status);
@@ -823,25 +879,18 @@ k_segment_det(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ pe
   for (int s = blockIdx.x * GPC + threadIdx.x / LPR; s < n_unique; s += gridDim.x * GPC) {
     const int b = static_cast<int>(seg_start[s]);
     const uint32_t key = skey[b];
-    for (int col0 = 0; col0 < d; col0 += COLS) {
+    bool is_long = false;
+    for (int col0 = 0; col0 < d && !is_long; col0 += COLS) {
       T acc[NV][EPV];
-      if constexpr (OP == UpdateOp::kSgd || OP == UpdateOp::kAddToTensor) {
-#pragma unroll
-        for (int k = 0; k < NV; ++k) {
-          const int col = col0 + (l + k * LPR) * EPV;
-          if (col < d) load_vec<T, VEC>(P.param + static_cast<int64_t>(key) * d + col, acc[k]);
-          else {
-#pragma unroll
-            for (int e = 0; e < EPV; ++e) acc[k][e] = T(0);
-          }
-        }
-      } else {
-        zero_acc<T, NV, EPV>(acc);  // MergeAdd starts from +0.0 (SetConstant, selected_rows_functor.cc:211-212)
-      }
+      det_begin<T, OP, LPR, NV, VEC>(P, key, col0, l, acc);
       T lr = T(0);
       if constexpr (OP == UpdateOp::kSgd) lr = *P.lr;
       bool more = true;
       for (int e0 = b; more; e0 += kPrefetch) {
+        if (e0 - b >= kLongSeg) {   // col0 == 0 here: a long row leaves on its first column slice
+          is_long = true;
+          break;
+        }
         T r[kPrefetch][NV][EPV];
         bool same[kPrefetch];
 #pragma unroll
@@ -861,30 +910,138 @@ k_segment_det(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ pe
         }
 #pragma unroll
         for (int q = 0; q < kPrefetch; ++q) {
-          if (more && same[q]) {
-#pragma unroll
-            for (int k = 0; k < NV; ++k)
-#pragma unroll
-              for (int e = 0; e < EPV; ++e) {
-                if constexpr (OP == UpdateOp::kSgd)
-                  acc[k][e] = A::sub(acc[k][e], A::mul(lr, r[q][k][e]));  // sgd_op.h:77-79
-                else
-                  acc[k][e] = A::add(acc[k][e], r[q][k][e]);
-              }
-          } else {
-            more = false;
-          }
+          if (more && same[q]) det_add<T, OP, NV, EPV>(acc, r[q], lr);
+          else more = false;
         }
       }
-      if constexpr (OP == UpdateOp::kSgd || OP == UpdateOp::kAddToTensor) {
+      if (!is_long) det_end<T, OP, LPR, NV, VEC>(P, key, static_cast<uint32_t>(b), col0, l, acc);
+    }
+    if (is_long && l == 0) long_list[atomicAdd(long_count, 1u)] = static_cast<uint32_t>(s);
+  }
+}
+
+// Long rows.  The adds of one ELEMENT of a row are a dependent chain, but the elements are independent, and one SM
+// pulls scattered rows out of HBM at a small fraction of the device bandwidth (its loads in flight divided by
+// the latency).  So a listed row is cut into column slices of kSliceLanes vectors (64 bytes for fp32), and
+// each (row, slice) pair is one work item with a CTA to itself: a hot row is fetched by several SMs at once,
+// and a CTA's 64 KB tile holds 1024 duplicates of a slice instead of 256 whole rows.  Thread (rr, l) fetches
+// duplicates rr, rr + RPP, ... of the tile into registers while the slice's first lanes add the previous tile
+// out of shared memory — in sorted (= input) order, which is all that bit-exactness needs; the sorted positions
+// of a tile are read one tile further ahead, so each tile costs one memory round trip, not two.
+// ctrs[0] = list length (reset by the last CTA to finish, ctrs[1] counts finished CTAs): both are zero again
+// when the kernel ends.
+template <bool VEC> struct LongDet {
+  static constexpr int kSliceLanes = VEC ? 4 : 16;   // lanes (vectors) per slice
+  static constexpr int kJ = 16;                      // duplicates in flight per thread
+};
+constexpr int kLongDetSmem = 64 * 1024;
+
+template <typename T, UpdateOp OP, bool VEC>
+__global__ void __launch_bounds__(kBlock, 1)
+k_long_segment_det(const uint32_t* __restrict__ skey, const uint32_t* __restrict__ perm, int n,
+                   const uint32_t* __restrict__ seg_start, const T* __restrict__ value, Params<T> P,
+                   const uint32_t* __restrict__ long_list, uint32_t* __restrict__ ctrs) {
+  constexpr int EPV = Epv<T, VEC>::value;
+  constexpr int SL = LongDet<VEC>::kSliceLanes;
+  constexpr int SC = SL * EPV;                     // columns per slice
+  constexpr int RPP = kBlock / SL;                 // duplicates per pass of the CTA
+  constexpr int J = LongDet<VEC>::kJ;
+  constexpr int R = RPP * J;                       // duplicates per tile
+  static_assert(R * SC * sizeof(T) <= kLongDetSmem, "tile fits the dynamic shared memory");
+  extern __shared__ __align__(16) unsigned char det_smem[];
+  T (*s_tile)[SC] = reinterpret_cast<T (*)[SC]>(det_smem);
+  __shared__ uint32_t s_cnt[2];
+  const int tid = threadIdx.x, rr = tid / SL, l = tid % SL;
+  const int d = P.d;
+  const uint32_t count = *reinterpret_cast<volatile uint32_t*>(ctrs);
+  const uint32_t slices = static_cast<uint32_t>((d + SC - 1) / SC);
+  T lr = T(0);
+  if constexpr (OP == UpdateOp::kSgd) lr = *P.lr;
+  for (uint32_t item = blockIdx.x; item < count * slices; item += gridDim.x) {
+    const int b = static_cast<int>(seg_start[long_list[item / slices]]);
+    const int col0 = static_cast<int>(item % slices) * SC;
+    const int col = col0 + l * EPV;                // this thread's columns
+    const uint32_t key = skey[b];
+    T acc[1][EPV];
+    if (rr == 0) det_begin<T, OP, SL, 1, VEC>(P, key, col0, l, acc);
+    T r[J][EPV];
+    uint32_t pos[J];                               // original positions of a tile's duplicates, kNoKey past the end
+    bool same[J];
+    auto fetch_pos = [&](int base) {
 #pragma unroll
-        for (int k = 0; k < NV; ++k) {
-          const int col = col0 + (l + k * LPR) * EPV;
-          if (col < d) store_vec<T, VEC>(P.param + static_cast<int64_t>(key) * d + col, acc[k]);
-        }
-      } else {
-        consume<T, OP, LPR, NV, VEC>(P, key, static_cast<uint32_t>(b), col0, l, acc);
+      for (int j = 0; j < J; ++j) {
+        const int idx = base + j * RPP + rr;
+        const bool in = idx < n;
+        const uint32_t k2 = in ? skey[idx] : ~key;
+        const uint32_t p2 = in ? perm[idx] : 0u;
+        pos[j] = k2 == key ? p2 : kNoKey;
       }
+    };
+    auto fetch = [&]() {
+#pragma unroll
+      for (int j = 0; j < J; ++j) {
+        same[j] = pos[j] != kNoKey;
+        if (same[j] && col < d) load_vec_stream<T, VEC>(value + static_cast<int64_t>(pos[j]) * d + col, r[j]);
+        else {
+#pragma unroll
+          for (int e = 0; e < EPV; ++e) r[j][e] = T(0);
+        }
+      }
+    };
+    fetch_pos(b);
+    fetch();
+    fetch_pos(b + R);
+    if (tid < 2) s_cnt[tid] = 0u;
+    __syncthreads();
+    int valid = R;                                 // duplicates in the tile being added; CTA-uniform
+    for (int t = 0; valid == R; ++t) {
+      uint32_t mine = 0;
+#pragma unroll
+      for (int j = 0; j < J; ++j) {
+        if constexpr (OP == UpdateOp::kSgd) {      // sgd_op.h:77-79: param -= lr * g, the product formed here
+#pragma unroll
+          for (int e = 0; e < EPV; ++e) r[j][e] = Arith<T>::mul(lr, r[j][e]);
+        }
+        store_vec<T, VEC>(&s_tile[j * RPP + rr][l * EPV], r[j]);
+        mine += same[j] ? 1u : 0u;
+      }
+      if (l == 0 && mine) atomicAdd(&s_cnt[t & 1], mine);
+      if (tid == 0) s_cnt[(t + 1) & 1] = 0u;       // last read before the previous tile's closing barrier
+      __syncthreads();
+      valid = static_cast<int>(s_cnt[t & 1]);      // a sorted run: the valid duplicates are rows [0, valid)
+      if (valid == R) {                            // a full tile: the row may go on
+        fetch();
+        fetch_pos(b + (t + 2) * R);
+      }
+      if (rr == 0) {
+        // the chain: a block of duplicates is read from shared memory back to back (ordered asm loads), then added
+        constexpr int KB = 16;
+        constexpr uint32_t kRowBytes = SC * sizeof(T);
+        const uint32_t mine_addr = smem_addr(det_smem) + l * EPV * static_cast<uint32_t>(sizeof(T));
+        int row = 0;
+        for (; row + KB <= valid; row += KB) {
+          T v[KB][1][EPV];
+#pragma unroll
+          for (int q = 0; q < KB; ++q) lds_vec(mine_addr + (row + q) * kRowBytes, v[q][0]);
+#pragma unroll
+          for (int q = 0; q < KB; ++q) det_add_scaled<T, OP, 1, EPV>(acc, v[q]);
+        }
+        for (; row < valid; ++row) {
+          T v[1][EPV];
+          lds_vec(mine_addr + row * kRowBytes, v[0]);
+          det_add_scaled<T, OP, 1, EPV>(acc, v);
+        }
+      }
+      __syncthreads();
+    }
+    if (rr == 0) det_end<T, OP, SL, 1, VEC>(P, key, static_cast<uint32_t>(b), col0, l, acc);
+  }
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence();
+    if (atomicAdd(ctrs + 1, 1u) == gridDim.x - 1) {
+      ctrs[0] = 0u;
+      ctrs[1] = 0u;
     }
   }
 }
@@ -908,9 +1065,31 @@ cudaError_t launch_op(const SortedPlan& plan, const T* value, int64_t n, int64_t
     constexpr int COLS = LPR * NV * Epv<T, VEC>::value;
     if (deterministic) {
       const int grid = static_cast<int>(std::min<int64_t>(ceil_div(n, GPC), 148 * 8));
+      // scratch of the fast path, idle in this mode: arrival words 0/1 (zero between launches) count the
+      // listed rows and the finished CTAs, the head-carry block holds the list (at most n / kLongSeg
+      // entries; the block has max_ctas * d elements >= n / 32 words)
+      uint32_t* ctrs = C.arrive;
+      uint32_t* list = reinterpret_cast<uint32_t*>(C.head);
+      const uint32_t* seg_start = reinterpret_cast<const uint32_t*>(ws + L.off_seg_start);
       k_segment_det<T, OP, LPR, NV, VEC><<<grid, kBlock, 0, s>>>(
-          plan.keys, plan.perm, ni, reinterpret_cast<const uint32_t*>(ws + L.off_seg_start),
-          reinterpret_cast<const PlanHeader*>(ws + L.off_plan), value, P);
+          plan.keys, plan.perm, ni, seg_start, reinterpret_cast<const PlanHeader*>(ws + L.off_plan), value, P,
+          list, ctrs);
+      if (n > kLongSeg) {
+        auto long_kern = k_long_segment_det<T, OP, VEC>;
+        static std::atomic<unsigned long long> long_attr_done{0};   // > 48 KB of dynamic shared memory: once per device
+        int dev = 0;
+        cudaGetDevice(&dev);
+        const unsigned long long bit = 1ull << (dev & 63);
+        if (!(long_attr_done.load(std::memory_order_relaxed) & bit)) {
+          if (cudaFuncSetAttribute(long_kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kLongDetSmem) !=
+              cudaSuccess) {
+            err = cudaGetLastError();
+            return;
+          }
+          long_attr_done.fetch_or(bit, std::memory_order_relaxed);
+        }
+        long_kern<<<148 * 2, kBlock, kLongDetSmem, s>>>(plan.keys, plan.perm, ni, seg_start, value, P, list, ctrs);
+      }
     } else {
       // one wave of lane groups at 3 CTAs per SM.  The chunk size fixes the summation tree, so it must
       // depend on (N, D) alone — not on the consumer (the fast-mode optimizers must reduce in exactly
@@ -925,19 +1104,13 @@ cudaError_t launch_op(const SortedPlan& plan, const T* value, int64_t n, int64_t
         const int c = ov ? std::atoi(ov) : 0;
         return (c >= 1 && c <= 4) ? c : 3;
       }();
-      static const int ring_target = [] {
-        const char* ov = std::getenv("B200EMB_RING_KB");
-        const int kb = ov ? std::atoi(ov) : 0;
-        return (kb >= 8 && kb <= 160) ? kb * 1024 : kRingTargetBytes;
-      }();
       const int chunk = chunk_override ? chunk_override : choose_chunk(n, GPC * cps);
       const int ctas = static_cast<int>(ceil_div(n, static_cast<int64_t>(GPC) * chunk));
       const int slack = std::min(kBoundarySlack, GPC * chunk / 2);
       using RG = Ring<T, OP, NV, VEC>;
-      const int batch = RG::batch_for(ring_target);
-      const size_t smem = RG::bytes_for(batch) + sizeof(T) * 2 * GPC * COLS +
+      const size_t smem = RG::kBytes + sizeof(T) * 2 * GPC * COLS +
                           sizeof(uint32_t) * (OP == UpdateOp::kMergeAdd ? 3 : 2) * (GPC * chunk + slack + 2);
-      const ChunkGeom G{ni, chunk, slack, batch};
+      const ChunkGeom G{ni, chunk, slack};
       auto kern = k_chunk_reduce<T, OP, LPR, NV, VEC>;
       // opt in to > 48 KB of dynamic shared memory once per device (the attribute is per device)
       static std::atomic<unsigned long long> attr_done{0};

@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--reps", type=int, default=200)
     ap.add_argument("--det", action="store_true", help="also time the bit-exact order mode")
     ap.add_argument("--tag", default="")
+    ap.add_argument("--det-only", action="store_true", help="three eager bit-exact-mode updates and nothing else (for ncu)")
     args = ap.parse_args()
     pkg = load_package()
     capi, synth = pkg.capi, pkg.synth
@@ -62,6 +63,12 @@ def main():
             capi.sparse_sgd(table, ids[b], grads[b], lr, ws[b], flags, status)
 
     stream = torch.cuda.Stream(dev)
+    if args.det_only:
+        for b in range(3):
+            update(b % nb, capi.DETERMINISTIC)
+        torch.cuda.synchronize()
+        print(json.dumps({"config": args.config, "det_only": True, "status_word": int(status.item())}))
+        return
 
     def phase(fn, reps):
         with torch.cuda.stream(stream):
