@@ -1074,7 +1074,7 @@ cudaError_t launch_op(const SortedPlan& plan, const T* value, int64_t n, int64_t
       k_segment_det<T, OP, LPR, NV, VEC><<<grid, kBlock, 0, s>>>(
           plan.keys, plan.perm, ni, seg_start, reinterpret_cast<const PlanHeader*>(ws + L.off_plan), value, P,
           list, ctrs);
-      if (n > kLongSeg) {
+      if (n >= kLongSeg) {   // a run of exactly kLongSeg duplicates is already handed over
         auto long_kern = k_long_segment_det<T, OP, VEC>;
         static std::atomic<unsigned long long> long_attr_done{0};   // > 48 KB of dynamic shared memory: once per device
         int dev = 0;

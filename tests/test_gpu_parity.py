@@ -453,6 +453,95 @@ def test_sparse_adagrad(capi, case, dtype):
     assert_bit_equal(host(m), em, "adagrad fast moment")
 
 
+# ------------------------------------------------------------------ bit-exact order mode, long rows
+# Rows with more than 64 duplicates leave k_segment_det for k_long_segment_det (one CTA per row and 64-byte column
+# slice, 1024-duplicate tiles for 16-byte-aligned widths, 256 otherwise): counts at and around the hand-over and
+# the tile sizes, widths with one / several / ragged slices, both load paths, every consumer.
+LONG_ROWS = [  # (duplicates of the hot id, other ids, d)
+    (64, 5, 4), (65, 5, 4), (255, 0, 7), (256, 3, 7), (257, 3, 31), (1023, 9, 64), (1024, 9, 64), (1025, 0, 64),
+    (2048, 50, 16), (3100, 50, 100), (700, 20, 203), (1500, 20, 260),
+]
+
+
+@pytest.mark.parametrize("case", LONG_ROWS, ids=lambda c: "dup%d_other%d_d%d" % c)
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_bit_exact_mode_long_rows(capi, case, dtype):
+    dup, other, d = case
+    v = 97
+    rng = np.random.default_rng(dup * 3 + d)
+    rows = np.concatenate([np.full(dup, 41, np.int64), rng.integers(0, v, size=other).astype(np.int64),
+                           np.full(dup // 2 + 70, 5, np.int64)])        # a second long row
+    rng.shuffle(rows)
+    grad = (rng.standard_normal((len(rows), d)) * 0.01).astype(dtype)
+    # MergeAdd
+    want_rows, want_val = oracle.merge_add(rows, grad)
+    r, val, u = capi.merge_add(dev(rows), dev(grad), v, flags=DET)
+    u = int(u.item())
+    assert u == len(want_rows) and np.array_equal(host(r)[:u], want_rows)
+    assert_bit_equal(host(val)[:u], want_val, "merge_add det, long rows")
+    # SelectedRowsAddToTensor
+    base = rng.standard_normal((v, d)).astype(dtype)
+    want = base.copy()
+    oracle.selected_rows_add_to_tensor(rows, grad, want)
+    t = dev(base)
+    capi.selected_rows_add_to_tensor(dev(rows), dev(grad), t, flags=DET)
+    assert_bit_equal(host(t), want, "add_to_tensor det, long rows")
+    # sgd
+    lr = np.array([0.01], dtype)
+    want = base.copy()
+    oracle.sgd_sparse(want, rows, grad, lr)
+    p = dev(base)
+    capi.sparse_sgd(p, dev(rows), dev(grad), dev(lr), flags=DET)
+    assert_bit_equal(host(p), want, "sgd det, long rows")
+    # adam
+    m10 = (rng.standard_normal((v, d)) * 1e-3).astype(dtype)
+    m20 = (rng.random((v, d)) * 1e-4).astype(dtype)
+    b1p, b2p = np.array([0.9 ** 2], dtype), np.array([0.999 ** 2], dtype)
+    wp, wm1, wm2 = base.copy(), m10.copy(), m20.copy()
+    oracle.adam_sparse(wp, wm1, wm2, rows, grad, lr, b1p, b2p)
+    p, m1, m2 = dev(base), dev(m10), dev(m20)
+    capi.sparse_adam(p, m1, m2, dev(rows), dev(grad), dev(lr), dev(b1p), dev(b2p), flags=DET)
+    assert_bit_equal(host(p), wp, "adam det param, long rows")
+    assert_bit_equal(host(m1), wm1, "adam det m1, long rows")
+    assert_bit_equal(host(m2), wm2, "adam det m2, long rows")
+    # adagrad
+    wp, wm = base.copy(), m20.copy()
+    oracle.adagrad_sparse(wp, wm, rows, grad, lr, 1e-6)
+    p, m = dev(base), dev(m20)
+    capi.sparse_adagrad(p, m, dev(rows), dev(grad), dev(lr), 1e-6, flags=DET)
+    assert_bit_equal(host(p), wp, "adagrad det param, long rows")
+    assert_bit_equal(host(m), wm, "adagrad det moment, long rows")
+    # one plan, several consumers on the same workspace (the fused wrappers' pattern): the long-row list and its
+    # counters live in scratch of the fast path and must be left the way the fast path expects them
+    ws = capi.alloc_workspace(len(rows), d, grad.itemsize)
+    drows, dgrad = dev(rows), dev(grad)
+    capi.plan_rows(drows, v, ws)
+    want = base.copy()
+    oracle.sgd_sparse(want, rows, grad, lr)
+    oracle.sgd_sparse(want, rows, grad, lr)
+    p = dev(base)
+    capi.sparse_sgd(p, drows, dgrad, dev(lr), workspace=ws, flags=DET | capi.PLAN_READY)
+    capi.sparse_sgd(p, drows, dgrad, dev(lr), workspace=ws, flags=DET | capi.PLAN_READY)
+    assert_bit_equal(host(p), want, "sgd det twice on one plan, long rows")
+    pf, pg = dev(base), dev(base)
+    capi.sparse_sgd(pf, drows, dgrad, dev(lr), workspace=ws, flags=capi.PLAN_READY)      # fast, after det, same plan
+    capi.sparse_sgd(pg, drows, dgrad, dev(lr))                                            # fast, fresh workspace
+    assert_bit_equal(host(pf), host(pg), "fast mode after bit-exact mode on one plan")
+
+
+def test_bit_exact_mode_run_of_exactly_the_handover_length(capi):
+    for n in (63, 64, 65):
+        rows = np.full(n, 3, np.int64)
+        grad = np.random.default_rng(n).standard_normal((n, 12)).astype(np.float32)
+        base = np.zeros((5, 12), np.float32)
+        want = base.copy()
+        lr = np.array([0.5], np.float32)
+        oracle.sgd_sparse(want, rows, grad, lr)
+        p = dev(base)
+        capi.sparse_sgd(p, dev(rows), dev(grad), dev(lr), flags=DET)
+        assert_bit_equal(host(p), want, "sgd det, %d duplicates and nothing else" % n)
+
+
 def test_cluster_sort_opt_in_path_matches_default():
     """B200EMB_CLUSTER_SORT=1 routes small plans through the single 16-CTA-cluster DSMEM sort
     (csrc/cluster_sort.cu).  The env var is read once per process, so the check runs in a child process:
