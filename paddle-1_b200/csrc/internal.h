@@ -17,7 +17,7 @@ constexpr int kScanTile = 2048;                        // head-flag scan tile
 
 // ---- segmented-reduce geometry (segreduce.cu) ------------------------------------------
 constexpr int kMinChunk = 4;     // sorted elements walked by one lane group, lower bound
-constexpr int kMaxChunk = 64;
+constexpr int kMaxChunk = 128;
 constexpr int kMinGroupsPerCta = 8;   // 256 threads / 32 lanes
 
 inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
@@ -158,7 +158,7 @@ cudaError_t launch_update(const SortedPlan& plan, const T* value, int64_t n, int
                           int64_t height, const UpdateArgs<T>& args, bool deterministic, char* ws,
                           const Workspace& L, int32_t* status, cudaStream_t s);
 
-int choose_chunk(int64_t n, int groups_per_sm);
+int choose_chunk(int64_t n, int groups_per_cta, int ctas_per_sm);
 
 // shard.cu
 cudaError_t launch_inverse_map(const SortedPlan& plan, const uint32_t* uidx, int64_t n, uint32_t* inv,

@@ -1104,7 +1104,7 @@ cudaError_t launch_op(const SortedPlan& plan, const T* value, int64_t n, int64_t
         const int c = ov ? std::atoi(ov) : 0;
         return (c >= 1 && c <= 4) ? c : 3;
       }();
-      const int chunk = chunk_override ? chunk_override : choose_chunk(n, GPC * cps);
+      const int chunk = chunk_override ? chunk_override : choose_chunk(n, GPC, cps);
       const int ctas = static_cast<int>(ceil_div(n, static_cast<int64_t>(GPC) * chunk));
       const int slack = std::min(kBoundarySlack, GPC * chunk / 2);
       using RG = Ring<T, OP, NV, VEC>;

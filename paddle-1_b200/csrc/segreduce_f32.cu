@@ -3,11 +3,15 @@
 
 namespace b200emb {
 
-int choose_chunk(int64_t n, int groups_per_sm) {
-  // one full wave of lane groups across the chip's 148 SMs, chunk clamped to [4, 64]
-  const int64_t target_groups = 148LL * groups_per_sm;
+int choose_chunk(int64_t n, int groups_per_cta, int ctas_per_sm) {
+  // one full wave of lane groups across the chip's 148 SMs when that fits a chunk of [4, 64]; batches that need
+  // more than 8 waves at 64 take up to 128 while a CTA stays within 1024 elements (fewer, longer CTAs: C5's update
+  // 1372 -> 1296 us; C3, 3 waves, is faster at 64).  A function of (N, D) alone, like everything about the geometry.
+  const int64_t target_groups = 148LL * groups_per_cta * ctas_per_sm;
   int64_t c = ceil_div(n, target_groups);
-  c = std::max<int64_t>(kMinChunk, std::min<int64_t>(kMaxChunk, c));
+  const int64_t cap = c > 8 * 64 ? std::max<int64_t>(kMaxChunk / 2, std::min<int64_t>(kMaxChunk, 1024 / groups_per_cta))
+                                 : kMaxChunk / 2;
+  c = std::max<int64_t>(kMinChunk, std::min<int64_t>(cap, c));
   return static_cast<int>(c);
 }
 
