@@ -96,6 +96,18 @@ def main():
         if len(cl):
             dt = (cl[:, 6] - cl[:, 5]) / 1e3
             print("  %-24s median %.2f  p90 %.2f  max %.2f us  (%d CTAs)" % ("close_chain", np.median(dt), np.percentile(dt, 90), dt.max(), len(cl)))
+        ids_live = np.nonzero(live)[0]
+        pro = (t[:, 1] - t[:, 0]) / 1e3
+        for j in np.argsort(-pro)[:6]:
+            print("    slow prologue: CTA %d  keys->smem %.2f  main %.2f  tail %.2f  arrival? %s close? %s" % (
+                ids_live[j], pro[j], (t[j, 2] - t[j, 1]) / 1e3, (t[j, 4] - t[j, 3]) / 1e3, t[j, 5] > 0, t[j, 6] > 0))
+        late = (t[:, 2] - t0) / 1e3
+        for j in np.argsort(-late)[:6]:
+            print("    late main-loop end: CTA %d  end %.2f  keys->smem %.2f  main %.2f" % (
+                ids_live[j], late[j], pro[j], (t[j, 2] - t[j, 1]) / 1e3))
+        m_end = (t[:, 2] - t0) / 1e3
+        print("  main-loop end after first start: p10 %.2f  median %.2f  p90 %.2f  max %.2f us" % (
+            np.percentile(m_end, 10), np.median(m_end), np.percentile(m_end, 90), m_end.max()))
         print("  time of last main-loop end %.2f us, last combine end %.2f us, last end %.2f us after first start" % (
             (t[:, 2].max() - t0) / 1e3, (t[:, 4].max() - t0) / 1e3, (end.max() - t0) / 1e3))
 
