@@ -380,6 +380,99 @@ def parity_epilogue(pkg, tab, zipf_seeded, v, d, rank, world, dev):
     return res
 
 
+# --------------------------------------------------------------------------- configs[4] at N GPUs
+def c5_sharded(pkg, rank, world, dev, peak, steps):
+    """BASELINE.json configs[4] on N GPUs: the duplicate-heavy batch (65536 x 100 Zipf(1.3) ids per GPU per step, one
+    id with ~1.67 M duplicates) on the 50M x 256 fp32 table row-sharded over the GPUs, sparse SGD, through the same
+    engine.  A timed run, then one checked step from a hashed table: the gathered rows must be the table's bits,
+    and sampled updated rows (the hottest id among them) must sit inside the reordering bound of the fp64 sum of
+    every rank's gradient rows for that id (partial sums per rank, all-reduced: nothing big crosses ranks)."""
+    from importlib import import_module
+    stepbench = import_module("paddle1_b200.stepbench")
+    capi, synth, sharded = pkg.capi, pkg.synth, pkg.sharded
+    v, d, n, a, opt = synth.CONFIGS["C5_dup_heavy"]
+    tab = sharded.ShardedTable(v, d, sharded.CudaOps(capi), dev)
+    stepbench.init_shard_hashed(tab.shard, rank, world, v)
+    lr = torch.tensor([0.01], dtype=torch.float32, device=dev)
+    zipf = synth.ZipfIds(v, a, seed=100 + rank)
+    use_graphs = os.environ.get("B200EMB_SHARD_NO_GRAPH") is None
+    r = measure(pkg, tab, zipf, n, d, rank, world, dev, steps, 4, lr, False, use_graphs)
+    # ---- one checked step
+    stepbench.init_shard_hashed(tab.shard, rank, world, v)
+    ids_np = zipf.sample(n)
+    ids = torch.from_numpy(ids_np).to(dev)
+    g = torch.Generator(device=dev)
+    g.manual_seed(777 + rank)
+    dout = torch.randn((n, d), device=dev, generator=g) * 0.01
+    n_s = 4097
+    if rank == 0:
+        u, c = np.unique(ids_np, return_counts=True)
+        pick = np.random.default_rng(5).choice(u, size=n_s - 1, replace=False)
+        samp = np.unique(np.concatenate([[u[np.argmax(c)]], pick]))
+        samp = np.concatenate([samp, np.full(n_s - len(samp), -1, np.int64)])
+        hot = int(c.max())
+    else:
+        samp, hot = np.zeros(n_s, np.int64), 0
+    st = torch.from_numpy(samp).to(dev)
+    dist.broadcast(st, 0)
+    samp_d = st[st >= 0]
+    idx = torch.searchsorted(samp_d, ids).clamp_(max=samp_d.numel() - 1)
+    hit = (samp_d[idx] == ids).nonzero().squeeze(1)
+    part = torch.zeros((samp_d.numel(), d), dtype=torch.float64, device=dev)
+    l1 = torch.zeros_like(part)
+    for lo in range(0, hit.numel(), 1 << 19):       # bounded temporaries: the hottest id alone has > 1 M matches
+        h = hit[lo:lo + (1 << 19)]
+        gd = dout[h].double()
+        part.index_add_(0, idx[h], gd)
+        l1.index_add_(0, idx[h], gd.abs())
+    dist.all_reduce(part)
+    dist.all_reduce(l1)
+    cap_recv, _ = recv_capacity([ids_np], world, rank)
+    tab.enable_engine(n, int(cap_recv * 1.25) + 1024)
+    torch.cuda.synchronize(dev)
+    dist.barrier()
+    prep = tab.prepare(ids, None)
+    out, ctx = tab.lookup(ids, None, prep=prep)
+    tab.update(ctx, dout, lr)
+    torch.cuda.synchronize(dev)
+    dist.barrier()
+    tab.check_status()
+    chk = torch.randint(0, n, (65536,), device=dev)
+    gather_ok = bool(torch.equal(out[chk].view(torch.int32), stepbench.hashed_rows(ids[chk], d).view(torch.int32)))
+    mine = samp_d % world == rank
+    init = stepbench.hashed_rows(samp_d[mine], d).double()
+    truth = init - 0.01 * part[mine]
+    got = tab.shard[samp_d[mine] // world].double()
+    bound = 1e-6 * (0.01 * l1[mine] + init.abs()) + 1e-30
+    rows_ok = bool(((got - truth).abs() <= bound).all().item())
+    moved = bool(((got - init).abs().amax(dim=1) > 0).all().item()) if int(mine.sum().item()) else True
+    flags = torch.tensor([int(gather_ok), int(rows_ok), int(moved)], device=dev)
+    dist.all_reduce(flags, op=dist.ReduceOp.MIN)
+    tab.engine.destroy()
+    tab.peer = False
+    ms = r["ms_per_step"]
+    b_req = n * (8 + 4 * d) + n * (8 + 4 * d)
+    b_own = r["recv_rows"] * (8 + 2 * 4 * d) + r["recv_rows"] * (8 + 4 * d) + r["recv_rows"] * 2 * 4 * d
+    hbm = (b_req + b_own) / (ms * 1e-3) / 1e9
+    nv = r["nvlink_out_bytes"] / (ms * 1e-3) / 1e9
+    entry = {"config": "C5_dup_heavy, row-sharded over %d GPUs" % world, "table": [v, d], "ids_per_gpu_per_step": n,
+             "optimizer": opt, "ms_per_step": ms, "value": r["value"], "unit": UNIT, "steps": steps,
+             "unique_ids_per_gpu": r["unique_local"], "rows_received_per_gpu": r["recv_rows"],
+             "cuda_graphs": r["graphs"], "phases_us": r["phases_us"],
+             "roofline": {"hbm_GBs_per_gpu": hbm, "hbm_frac": hbm / peak, "nvlink_GBs_per_direction": nv,
+                          "nvlink_frac": nv / NVLINK_GBS},
+             "parity": {"checked": "one step from a hashed table: 65536 gathered rows bit-exact; %d sampled updated rows "
+                                   "(incl. the hottest id, %d duplicates on rank 0 alone) within 1e-6 * (lr * sum|g| + |p|) "
+                                   "of the fp64 sum over every rank's gradient rows; bit-exact mode not run at this size"
+                                   % (int(samp_d.numel()), hot),
+                        "gather_bit_exact": bool(flags[0].item()), "fast_rows_within_bound": bool(flags[1].item()),
+                        "sampled_rows_updated": bool(flags[2].item()),
+                        "ok": bool(flags.min().item())}}
+    del tab, ids, dout, out, part, l1
+    torch.cuda.empty_cache()
+    return entry
+
+
 def run(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -425,6 +518,14 @@ def run(args):
         return z
     parity = parity_epilogue(pkg, tab, zipf_seeded, v, d, rank, world, dev)
     ok = parity["fast_ok"] and parity["det_bit_exact"]
+    hs_rows = tab.hs
+    extra = []
+    if not quick and os.environ.get("B200EMB_BENCH_NO_C5") is None:
+        del tab.shard                  # configs[4] needs the room: 51 GB / N per GPU plus 4 x 13.4 GB of batch buffers
+        torch.cuda.empty_cache()
+        c5 = c5_sharded(pkg, rank, world, dev, peak, max(4, min(args.steps, 8)))
+        extra.append(c5)
+        ok = ok and c5["parity"]["ok"]
 
     if rank == 0:
         def roof(r):
@@ -463,7 +564,7 @@ def run(args):
                        "mode": "fast (fixed-tree reduction), duplicates merged before they cross NVLink; row-sharded "
                                "engine b200emb_shard_*: peer stores + per-source arrival flags, no collective, no host read",
                        "l2": "inputs rotate over %d batch buffers per GPU (%.0f MB) > 126 MB L2 for the sweep sizes; "
-                             "the shard is %.1f GB" % (N_ROTATE, N_ROTATE * n_main * (8 + 8 * d) / 1e6, tab.hs * d * 4 / 1e9),
+                             "the shard is %.1f GB" % (N_ROTATE, N_ROTATE * n_main * (8 + 8 * d) / 1e6, hs_rows * d * 4 / 1e9),
                        "launch": ("CUDA graphs per batch buffer (prepare | lookup+update); " if main["graphs"] else "eager launches; ") +
                                  "the ids-only part of step i+1 (sort plan, de-duplication) runs on a side stream during "
                                  "step i (data-loader prefetch); every step still does one of each"},
@@ -474,7 +575,7 @@ def run(args):
                                     "frac": rf["nvlink_frac"]}},
             "e2e": main["e2e"], "phases_us": main["phases_us"], "gpu_launches": launches * args.steps,
             "one_gpu_same_batch": base.get(n_main), "sweep": [entry(main)] + [entry(r) for r in sweep],
-            "parity": parity,
+            "parity": parity, "configs_extra": extra,
         }
         if n_main in base:
             line["speedup_vs_one_gpu_same_batch"] = main["value"] / base[n_main]["value"]
@@ -483,4 +584,4 @@ def run(args):
     dist.barrier()
     dist.destroy_process_group()
     if not ok:
-        raise SystemExit("sharded parity epilogue FAILED: %s" % json.dumps(parity))
+        raise SystemExit("sharded parity FAILED: %s %s" % (json.dumps(parity), json.dumps([e["parity"] for e in extra])))

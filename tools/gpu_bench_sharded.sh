@@ -15,3 +15,15 @@ try:
 except Exception as e:
     print('parse failed', e)
 PY
+python - <<PY
+import json
+try:
+    r=json.loads(open('gpurun_out/r2_sh${N}_full.json').read().strip().splitlines()[-1])
+    for e in r.get('configs_extra', []):
+        print(e['config'], 'ms %.3f value %.3g' % (e['ms_per_step'], e['value']), 'unique', e['unique_ids_per_gpu'], 'recv', e['rows_received_per_gpu'], 'hbm %.3f nvl %.3f' % (e['roofline']['hbm_frac'], e['roofline']['nvlink_frac']), 'graphs', e['cuda_graphs'])
+        print('   parity', {k: v for k, v in e['parity'].items() if k != 'checked'})
+        for k, v in e['phases_us'].items(): print('   %8.1f us  %s' % (v, k))
+except Exception as e:
+    print('parse failed', e)
+PY
+tail -5 gpurun_out/r2_sh${N}_full.err | cut -c1-300
