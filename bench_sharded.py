@@ -8,7 +8,9 @@ The step goes through the C ABI's row-sharded engine (b200emb_shard_*): no colle
 After the timed runs a checked epilogue replays 8 consecutive steps (prefetch pipeline on) in the fast and in
 the bit-exact mode and compares them with the oracle run on the concatenated id streams of all ranks; the
 line carries the result in `parity` and the process exits non-zero if it fails.  (bench code: the oracle is
-used here as the checker only, never on the timed path.)
+used here as the checker only, never on the timed path.)  Last, BASELINE.json configs[4] — 50M x 256 table,
+65536 x 100 duplicate-heavy ids per GPU — runs row-sharded over the same GPUs as a `configs_extra` entry with
+its own checked step (c5_sharded); B200EMB_BENCH_NO_C5=1 or B200EMB_BENCH_QUICK=1 skip it.
 """
 import json
 import os
