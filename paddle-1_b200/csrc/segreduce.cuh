@@ -253,7 +253,8 @@ __device__ __forceinline__ void close_chain(int c, int len, uint32_t key, uint32
   const int d = P.d;
   for (int col0 = 0; col0 < d; col0 += COLS) {
     T sum[NV][EPV];
-    if (g == 0) {  // tail row: issued before the head rows so the loads overlap
+    RowState<T, OP, NV, EPV> st;
+    if (g == 0) {  // tail row and the row's state: issued before the head rows so all these loads overlap
 #pragma unroll
       for (int k = 0; k < NV; ++k) {
         const int col = col0 + (l + k * LPR) * EPV;
@@ -263,6 +264,7 @@ __device__ __forceinline__ void close_chain(int c, int len, uint32_t key, uint32
           for (int e = 0; e < EPV; ++e) sum[k][e] = T(0);
         }
       }
+      load_state<T, OP, LPR, NV, VEC>(P, key, col0, l, st);
     }
     T part[NV][EPV];
     zero_acc<T, NV, EPV>(part);
@@ -304,7 +306,7 @@ __device__ __forceinline__ void close_chain(int c, int len, uint32_t key, uint32
 #pragma unroll
           for (int e = 0; e < EPV; ++e)
             sum[k][e] = A::add(sum[k][e], s_part[j * COLS + (l + k * LPR) * EPV + e]);
-      consume<T, OP, LPR, NV, VEC>(P, key, eref, col0, l, sum);
+      apply_state<T, OP, LPR, NV, VEC>(P, key, eref, col0, l, sum, st);
     }
     __syncthreads();
   }
@@ -756,27 +758,30 @@ __device__ __forceinline__ void chunk_reduce_body(const uint32_t* __restrict__ s
     // Every thread's carry stores happen before the barrier above; this one fence (cumulative) publishes
     // them device-wide before the CTA counts itself in — the grid-sync idiom, one MEMBAR per CTA instead of 256.
     __threadfence();
+    // both arrivals are issued before either count is read: one round trip, not two, for a CTA that a segment
+    // enters and another one leaves
+    const int c0 = cta - s_before, members = s_before + (through ? s_after : 0) + 1;
+    uint32_t seen_head = 0, seen_tail = 0;
+    if (has_head) seen_head = atomicAdd(C.arrive + c0, 1u);
+    if (has_tail) seen_tail = atomicAdd(C.arrive + cta, 1u);
     int nfix = 0;
-    if (has_head) {
-      const int c0 = cta - s_before, members = s_before + (through ? s_after : 0) + 1;
-      if (atomicAdd(C.arrive + c0, 1u) == static_cast<uint32_t>(members - 1)) {
-        s_fix_c[nfix] = c0;
-        s_fix_len[nfix++] = members - 1;
-      }
+    if (has_head && seen_head == static_cast<uint32_t>(members - 1)) {
+      s_fix_c[nfix] = c0;
+      s_fix_len[nfix++] = members - 1;
     }
-    if (has_tail) {
-      if (atomicAdd(C.arrive + cta, 1u) == static_cast<uint32_t>(s_after)) {
-        s_fix_c[nfix] = cta;
-        s_fix_len[nfix++] = s_after;
-      }
+    if (has_tail && seen_tail == static_cast<uint32_t>(s_after)) {
+      s_fix_c[nfix] = cta;
+      s_fix_len[nfix++] = s_after;
     }
+    // the other members' carry rows were published before their arrivals: this fence, by the thread that observed
+    // them, and the barrier below order the closing loads (L2 loads, ld.cg) of every thread after them
+    if (nfix) __threadfence();
     s_nfix = nfix;
   }
   __syncthreads();
   const int nfix = s_nfix;
   B200EMB_STAMP(5);
   if (nfix == 0) return;
-  __threadfence();                       // the other members' carry rows, published before their arrivals
   for (int f = 0; f < nfix; ++f) {
     const int c0 = s_fix_c[f];
     const bool own_tail = c0 == cta;     // the chain that starts here; otherwise the one that entered
