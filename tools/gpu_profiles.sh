@@ -14,3 +14,8 @@ $CMD3 > gpurun_out/r2_plain3.log 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:"k_chunk_reduce" -s 4 -c 3 -o gpurun_out/r2_prof_c3 -f $CMD3 > gpurun_out/r2_ncu3.log 2>&1
 echo "full c3 rc=$?"
 ls -la gpurun_out/*.ncu-rep gpurun_out/r2_launches_cold.csv
+# bit-exact order mode kernels (C2)
+CMD4="python tools/phase_bench.py C2_ctr_sgd --det-only"
+$CMD4 > gpurun_out/r2_plain4.log 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:"k_long_segment_det|k_segment_det" -c 4 -o gpurun_out/r2_prof_det -f $CMD4 > gpurun_out/r2_ncu4.log 2>&1
+echo "full det rc=$?"
