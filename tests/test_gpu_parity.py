@@ -542,6 +542,37 @@ def test_bit_exact_mode_run_of_exactly_the_handover_length(capi):
         assert_bit_equal(host(p), want, "sgd det, %d duplicates and nothing else" % n)
 
 
+# ------------------------------------------------------------------ committed outputs of the reference kernels
+def test_bit_exact_mode_matches_committed_outputs_of_the_reference_kernels(capi, ref_fixtures):
+    """The CUDA path against tests/golden/ref_outputs.npz directly — what the reference's unmodified CPU kernels
+    produced on these seeded inputs — with no restatement in between."""
+    mod, store = ref_fixtures
+    for case in mod.CASES:
+        for dt in mod.DTYPES:
+            x = mod.inputs(*case, dt)
+            v = x["table"].shape[0]
+            want = lambda name: store[mod.key(case, dt, name)]
+            rows, value, lr = dev(x["rows"]), dev(x["value"]), dev(x["lr"])
+            assert np.array_equal(mod.bits(host(capi.lookup_table(dev(x["table"]), rows))), want("lookup"))
+            out = capi.lookup_table(dev(x["table"]), rows, int(x["rows"][-1]))
+            assert np.array_equal(mod.bits(host(out)), want("lookup_pad"))
+            r, val, u = capi.merge_add(rows, value, v, flags=DET)
+            u = int(u.item())
+            assert np.array_equal(host(r)[:u], want("merge_rows"))
+            assert np.array_equal(mod.bits(host(val)[:u]), want("merge_value"))
+            t = dev(x["table"])
+            capi.selected_rows_add_to_tensor(rows, value, t, flags=DET)
+            assert np.array_equal(mod.bits(host(t)), want("add_to_tensor"))
+            p = dev(x["table"])
+            capi.sparse_sgd(p, rows, value, lr, flags=DET)
+            assert np.array_equal(mod.bits(host(p)), want("sgd"))
+            p, m1, m2 = dev(x["table"]), dev(x["m1"]), dev(x["m2"])
+            capi.sparse_adam(p, m1, m2, rows, value, lr, dev(x["b1p"]), dev(x["b2p"]), flags=DET)
+            assert np.array_equal(mod.bits(host(p)), want("adam_p"))
+            assert np.array_equal(mod.bits(host(m1)), want("adam_m1"))
+            assert np.array_equal(mod.bits(host(m2)), want("adam_m2"))
+
+
 def test_cluster_sort_opt_in_path_matches_default():
     """B200EMB_CLUSTER_SORT=1 routes small plans through the single 16-CTA-cluster DSMEM sort
     (csrc/cluster_sort.cu).  The env var is read once per process, so the check runs in a child process:

@@ -282,3 +282,25 @@ def test_g11_regulariser_ops(goldens):
     assert (got == grad + np.float32(0.01) * tab[r]).all()
     with pytest.raises(IndexError):
         oracle.sparse_decay(tab, [8], 0.01)
+
+
+def test_oracle_matches_committed_outputs_of_the_reference_kernels(ref_fixtures):
+    """tests/golden/ref_outputs.npz holds what the reference's unmodified CPU kernels (oracle/_ref) produced on
+    seeded inputs; the restatement must reproduce every bit — on any machine, with or without /root/reference."""
+    mod, store = ref_fixtures
+    checked = 0
+    for case in mod.CASES:
+        for dt in mod.DTYPES:
+            x = mod.inputs(*case, dt)
+            got = mod.outputs(oracle, x, adam_kwargs={"reference_form": True})
+            for name, arr in got.items():
+                want = store[mod.key(case, dt, name)]
+                assert np.array_equal(mod.bits(arr), want), (case, np.dtype(dt).name, name)
+                checked += 1
+            # the restatement's default Adam form and both MergeAdd forms give the same bits as well
+            a = [x["table"].copy(), x["m1"].copy(), x["m2"].copy()]
+            oracle.adam_sparse(a[0], a[1], a[2], x["rows"], x["value"], x["lr"], x["b1p"], x["b2p"])
+            assert np.array_equal(mod.bits(a[0]), store[mod.key(case, dt, "adam_p")])
+            _, mv = oracle.merge_add(x["rows"], x["value"], reference_form=True)
+            assert np.array_equal(mod.bits(mv), store[mod.key(case, dt, "merge_value")])
+    assert checked == len(store.files)
