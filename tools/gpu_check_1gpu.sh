@@ -8,7 +8,7 @@ python -c "
 import json
 r=json.loads(open('gpurun_out/r2_bench17.json').read().strip().splitlines()[-1])
 print('ms/step %.4f' % r['ms_per_step'], 'det', r.get('det_ms_per_step'), 'value %.3g' % r['value'])
-print(json.dumps(r.get("parity"))[:300])
+print(json.dumps(r.get('parity'))[:300])
 for c in r.get('configs_extra', []): print(json.dumps(c)[:400])
 "
 tail -3 gpurun_out/r2_bench17.err | cut -c1-300
